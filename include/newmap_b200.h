@@ -1,0 +1,136 @@
+/* newmap_b200.h -- C-ABI of the B200-native `newmap search` hot path.
+ *
+ * One shared library (newmap_b200/libnewmap_b200.so, hand-written CUDA for sm_100a) that a
+ * host program binds with ctypes / dlopen.  Plain pointers and sizes only; all buffers passed in
+ * are HOST buffers owned by the caller unless a function says otherwise.  Every function
+ * returns an int: >= 0 success, < 0 one of the NM_E* codes (nm_strerror()).  There is no CPU
+ * fallback: without a usable CUDA device nm_index_open fails with NM_ECUDA.
+ *
+ * Reference interfaces replaced (paths relative to hoffmangroup/newmap):
+ *   src/newmap-count.c:9-17,136    createIndex / awFmReadIndexFromFile    -> nm_index_open
+ *   src/newmap-count.c:202-203     awFmDeallocIndex                        -> nm_index_close
+ *   src/newmap-count.c:91-206      count_kmers_from_sequence               -> nm_count_from_sequence
+ *   src/newmap-count.c:28-89       count_kmers                             -> nm_count_from_sequence
+ *                                                                             (k-mers concatenated by the caller)
+ *   AvxWindowFmIndex/src/AwFmParallelSearch.c:136-255  awFmParallelSearchCount -> the kernels behind both
+ *   newmap/search.py:383-548       binary_search (+ :647-724 get_kmer_counts,
+ *                                  :744-871 ambiguity mask / upper bounds) -> nm_min_unique (mode NM_MODE_RANGE)
+ *   newmap/search.py:551-644       linear_search                           -> nm_min_unique (mode NM_MODE_LIST)
+ */
+#ifndef NEWMAP_B200_H
+#define NEWMAP_B200_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NM_ABI_VERSION 1
+
+/* error codes (negative = failure, mirroring enum AwFmReturnCode's sign convention,
+ * AvxWindowFmIndex/src/AwFmIndex.h:131-137) */
+#define NM_OK 0
+#define NM_EOPEN (-1)      /* index file could not be opened */
+#define NM_EFORMAT (-2)    /* not an .awfmi file / truncated / inconsistent header */
+#define NM_EVERSION (-3)   /* .awfmi version != 8 or alphabet != DNA */
+#define NM_EALLOC (-4)     /* host or device allocation failed */
+#define NM_ESHORT (-5)     /* short read */
+#define NM_EARG (-6)       /* invalid argument (empty k-mer, index+length beyond the sequence, ...) */
+#define NM_ECUDA (-7)      /* CUDA runtime error; nm_last_cuda_error() has the text */
+#define NM_EUNSUPPORTED (-8)
+
+#define NM_MODE_RANGE 0    /* klist = {min_k, max_k}: minimum over every k in [min_k, max_k] */
+#define NM_MODE_LIST 1     /* klist = explicit lengths, tried in the order given */
+
+#define NM_ALGO_AUTO 0       /* trajectory-free search (result identical to the reference's) and, if it
+                                meets a k-mer absent from the index, a replay on the reference's
+                                trajectory so that the reported k-mer is the reference's */
+#define NM_ALGO_TRAJECTORY 1 /* the reference's own query trajectory (binary / linear search of
+                                search.py), one thread per position */
+#define NM_ALGO_FREE_GENERIC 2 /* trajectory-free search forced onto the unmodified .awfmi block layout */
+
+typedef struct nm_index nm_index;
+typedef struct nm_workspace nm_workspace;
+
+typedef struct nm_index_info {
+  uint64_t bwt_length;
+  uint64_t n_blocks;        /* 160-byte .awfmi blocks */
+  uint64_t prefix_sums[6];
+  uint64_t device_bytes;    /* HBM held by this index */
+  uint32_t seed_length;
+  uint32_t sa_compression_ratio;
+  uint32_t has_rank32;      /* 1 when the 32-byte rank layout was built (bwt_length < 2^32-1) */
+  int32_t device;
+} nm_index_info;
+
+typedef struct nm_stats {
+  uint64_t positions;         /* num_kmers of the call */
+  uint64_t lf_steps;          /* backward-extension steps executed on the device */
+  uint64_t queries;           /* (position,length) count queries executed (trajectory algo) */
+  uint64_t generic_searches;  /* searches routed to the unmodified-layout kernel (x letters, exceptions ...) */
+  uint64_t ref_lf_steps;      /* LF steps the reference's trajectory would have executed (0 if not computed) */
+  int64_t zero_pos;           /* first (round, position) whose two-strand count was 0, else -1 */
+  int64_t zero_len;
+  int64_t zero_round;
+  uint32_t algo_used;         /* NM_ALGO_* that produced the output */
+  uint32_t replayed;          /* 1 if NM_ALGO_AUTO fell back to the trajectory replay */
+  float ms_h2d, ms_prep, ms_search, ms_generic, ms_resolve, ms_d2h, ms_total; /* CUDA-event times of this call */
+} nm_stats;
+
+int nm_abi_version(void);
+const char *nm_strerror(int code);
+const char *nm_last_cuda_error(void);
+int nm_device_count(void);              /* >= 0, or NM_ECUDA */
+
+/* Reads header, BWT blocks, prefix sums and seed table of a reference-built .awfmi (v8, DNA;
+ * AvxWindowFmIndex/src/AwFmFile.c:174-409; the suffix array and FastaVector sections are not
+ * read), uploads them unchanged to `device` and derives the 32-byte rank layout there. */
+int nm_index_open(const char *path, int device, nm_index **out);
+void nm_index_close(nm_index *ix);
+int nm_index_info_get(const nm_index *ix, nm_index_info *info);
+
+/* counts[q] = occurrences of seq[idx[q] : idx[q]+len[q]] in the indexed text (u32, five-letter
+ * alphabet a c g t/u x exactly like AwFmParallelSearch.c:136-255).  reverse_complement != 0
+ * counts the k-mer newmap builds for the other strand (search.py:22,682-689).  Returns NM_EARG
+ * if any len[q]==0 or idx[q]+len[q] > seq_len (nothing is launched).  lf_steps may be NULL. */
+int nm_count_from_sequence(nm_index *ix, const uint8_t *seq, uint64_t seq_len, const uint64_t *idx,
+                           const uint64_t *len, uint64_t n, int reverse_complement, uint32_t *counts,
+                           uint64_t *lf_steps);
+
+/* One segment buffer of search.py (data = num_kmers start positions + look-ahead):
+ * out[i], i < num_kmers, = minimum unique length or 0, written as uint8/16/32 (out_width 1/2/4).
+ * stats may be NULL.  A two-strand count of 0 is NOT an error here: it is reported in
+ * stats->zero_* and the caller raises (search.py:699-722). */
+int nm_min_unique(nm_index *ix, const uint8_t *seg, uint64_t seg_len, uint64_t num_kmers, int mode,
+                  const uint32_t *klist, uint32_t nk, uint32_t initial_search_length, int use_rc,
+                  int algo, int out_width, void *out, nm_stats *stats);
+
+/* ---- pipelined / device-resident form of nm_min_unique -------------------------------------
+ * A workspace owns one CUDA stream and device scratch for segments up to max_seg_len bytes.
+ * upload/search/download are asynchronous on that stream; sync waits and fills stats.  Several
+ * workspaces on one index overlap copies with kernels.  `cuda_stream` may be a cudaStream_t
+ * created by the caller (e.g. torch's) or NULL to let the library create one. */
+int nm_workspace_create(nm_index *ix, uint64_t max_seg_len, void *cuda_stream, nm_workspace **out);
+void nm_workspace_destroy(nm_workspace *ws);
+int nm_workspace_upload(nm_workspace *ws, const uint8_t *seg, uint64_t seg_len);
+int nm_workspace_search(nm_workspace *ws, uint64_t num_kmers, int mode, const uint32_t *klist, uint32_t nk,
+                        uint32_t initial_search_length, int use_rc, int algo, int out_width);
+int nm_workspace_download(nm_workspace *ws, void *out);   /* num_kmers * out_width bytes of the last search */
+int nm_workspace_sync(nm_workspace *ws, nm_stats *stats);
+/* 64-bit FNV-style checksum of the last search's output computed on the device (for
+ * device-resident runs that never copy the output back). */
+int nm_workspace_checksum(nm_workspace *ws, uint64_t *sum);
+
+/* Pinned host memory for segment / output staging (cudaHostAlloc / cudaFreeHost). */
+void *nm_host_alloc(uint64_t bytes);
+void nm_host_free(void *p);
+
+/* Random-access roofline probe: `chains` independent dependent-load chains of `steps` loads of
+ * `granule` bytes (32, 64 or 128, granule-aligned) at pseudo-random offsets of a `bytes`-sized
+ * device buffer.  Returns loads/second measured with CUDA events. */
+int nm_probe_random_access(int device, uint64_t bytes, uint32_t granule, uint64_t chains, uint32_t steps,
+                           double *loads_per_second, float *ms);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

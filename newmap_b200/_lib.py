@@ -1,0 +1,298 @@
+"""ctypes binding of libnewmap_b200.so (include/newmap_b200.h).
+
+The library is hand-written CUDA for sm_100a; there is no CPU fallback.  Importing this module
+never touches the GPU; opening an index does, and raises if no CUDA device is usable."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from pathlib import Path
+
+import numpy as np
+
+PKG_DIR = Path(__file__).resolve().parent
+LIB_PATH = PKG_DIR / "libnewmap_b200.so"
+
+NM_MODE_RANGE, NM_MODE_LIST = 0, 1
+NM_ALGO_AUTO, NM_ALGO_TRAJECTORY, NM_ALGO_FREE_GENERIC = 0, 1, 2
+ALGOS = {"auto": NM_ALGO_AUTO, "trajectory": NM_ALGO_TRAJECTORY, "free_generic": NM_ALGO_FREE_GENERIC}
+NM_EOPEN, NM_EFORMAT, NM_EVERSION, NM_EALLOC, NM_ESHORT, NM_EARG, NM_ECUDA, NM_EUNSUPPORTED = range(-1, -9, -1)
+
+
+class IndexInfo(C.Structure):
+    _fields_ = [("bwt_length", C.c_uint64), ("n_blocks", C.c_uint64), ("prefix_sums", C.c_uint64 * 6),
+                ("device_bytes", C.c_uint64), ("seed_length", C.c_uint32), ("sa_compression_ratio", C.c_uint32),
+                ("has_rank32", C.c_uint32), ("device", C.c_int32)]
+
+
+class Stats(C.Structure):
+    _fields_ = [("positions", C.c_uint64), ("lf_steps", C.c_uint64), ("queries", C.c_uint64),
+                ("generic_searches", C.c_uint64), ("ref_lf_steps", C.c_uint64), ("zero_pos", C.c_int64),
+                ("zero_len", C.c_int64), ("zero_round", C.c_int64), ("algo_used", C.c_uint32),
+                ("replayed", C.c_uint32), ("ms_h2d", C.c_float), ("ms_prep", C.c_float), ("ms_search", C.c_float),
+                ("ms_generic", C.c_float), ("ms_resolve", C.c_float), ("ms_d2h", C.c_float), ("ms_total", C.c_float)]
+
+    def as_dict(self) -> dict:
+        return {name: getattr(self, name) for name, _ in self._fields_}
+
+
+# every symbol include/newmap_b200.h declares: (restype, argtypes)
+_vp, _u64, _u32, _i = C.c_void_p, C.c_uint64, C.c_uint32, C.c_int
+SIGNATURES = {
+    "nm_abi_version": (_i, []),
+    "nm_strerror": (C.c_char_p, [_i]),
+    "nm_last_cuda_error": (C.c_char_p, []),
+    "nm_device_count": (_i, []),
+    "nm_index_open": (_i, [C.c_char_p, _i, C.POINTER(_vp)]),
+    "nm_index_close": (None, [_vp]),
+    "nm_index_info_get": (_i, [_vp, C.POINTER(IndexInfo)]),
+    "nm_count_from_sequence": (_i, [_vp, _vp, _u64, _vp, _vp, _u64, _i, _vp, C.POINTER(_u64)]),
+    "nm_min_unique": (_i, [_vp, _vp, _u64, _u64, _i, _vp, _u32, _u32, _i, _i, _i, _vp, C.POINTER(Stats)]),
+    "nm_workspace_create": (_i, [_vp, _u64, _vp, C.POINTER(_vp)]),
+    "nm_workspace_destroy": (None, [_vp]),
+    "nm_workspace_upload": (_i, [_vp, _vp, _u64]),
+    "nm_workspace_search": (_i, [_vp, _u64, _i, _vp, _u32, _u32, _i, _i, _i]),
+    "nm_workspace_download": (_i, [_vp, _vp]),
+    "nm_workspace_sync": (_i, [_vp, C.POINTER(Stats)]),
+    "nm_workspace_checksum": (_i, [_vp, C.POINTER(_u64)]),
+    "nm_host_alloc": (_vp, [_u64]),
+    "nm_host_free": (None, [_vp]),
+    "nm_probe_random_access": (_i, [_i, _u64, _u32, _u64, _u32, C.POINTER(C.c_double), C.POINTER(C.c_float)]),
+}
+
+_lib = None
+
+
+def load() -> C.CDLL:
+    """dlopen the in-tree library; fails loudly when it has not been built."""
+    global _lib
+    if _lib is None:
+        if not LIB_PATH.is_file():
+            raise ImportError(f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; "
+                              f"g.build()'` or `make -C newmap_b200/csrc` (there is no CPU fallback)")
+        L = C.CDLL(str(LIB_PATH))
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(L, name)
+            fn.restype, fn.argtypes = res, args
+        if L.nm_abi_version() != 1:
+            raise ImportError("libnewmap_b200.so ABI version mismatch")
+        _lib = L
+    return _lib
+
+
+class NewmapError(RuntimeError):
+    def __init__(self, code: int, what: str):
+        L = load()
+        msg = L.nm_strerror(code).decode()
+        if code == NM_ECUDA:
+            msg += f" ({L.nm_last_cuda_error().decode()})"
+        super().__init__(f"{what}: {msg}")
+        self.code = code
+
+
+def check(code: int, what: str) -> int:
+    if code < 0:
+        if code in (NM_EOPEN, NM_EFORMAT, NM_EVERSION, NM_ESHORT):
+            # newmap-count.c:13-16: index load failures surface as OSError
+            raise OSError(f"Could not load reference index from file ({load().nm_strerror(code).decode()})")
+        if code == NM_EALLOC:
+            raise MemoryError(what)
+        raise NewmapError(code, what)
+    return code
+
+
+def as_u8(buf) -> np.ndarray:
+    """Zero-copy uint8 view of a bytes-like object (TypeError for str, like the 'y#' format of
+    newmap-count.c:102)."""
+    if isinstance(buf, str):
+        raise TypeError("a bytes-like object is required, not 'str'")
+    a = np.frombuffer(buf, dtype=np.uint8) if not isinstance(buf, np.ndarray) else buf
+    if a.dtype != np.uint8 or not a.flags.c_contiguous:
+        a = np.ascontiguousarray(a, dtype=np.uint8)
+    return a
+
+
+def out_dtype(max_k: int):
+    # search.py:204-212
+    if max_k <= 0xFF:
+        return np.dtype(np.uint8), "uint8"
+    if max_k <= 0xFFFF:
+        return np.dtype(np.uint16), "uint16"
+    return np.dtype(np.uint32), "uint32"
+
+
+class Index:
+    """A reference-built .awfmi resident in the HBM of one GPU (opened once, not once per call
+    like newmap-count.c:9-17,136)."""
+
+    def __init__(self, path, device: int | None = None):
+        L = load()
+        if device is None:
+            device = int(os.environ.get("NEWMAP_B200_DEVICE", os.environ.get("LOCAL_RANK", "0")))
+        h = _vp()
+        check(L.nm_index_open(os.fsencode(str(path)), device, C.byref(h)), f"nm_index_open({path})")
+        self._h = h
+        self.path = str(path)
+        self.device = device
+        info = IndexInfo()
+        check(L.nm_index_info_get(self._h, C.byref(info)), "nm_index_info_get")
+        self.info = info
+
+    def close(self):
+        if getattr(self, "_h", None):
+            load().nm_index_close(self._h)
+            self._h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def seed_length(self) -> int:
+        return int(self.info.seed_length)
+
+    @property
+    def bwt_length(self) -> int:
+        return int(self.info.bwt_length)
+
+    def count(self, seq, idx, length, reverse_complement: bool = False, return_steps: bool = False):
+        """u32 occurrence counts of seq[idx[q]:idx[q]+length[q]] (nm_count_from_sequence)."""
+        s = as_u8(seq)
+        idx = np.ascontiguousarray(idx, dtype=np.uint64)
+        length = np.ascontiguousarray(length, dtype=np.uint64)
+        if idx.shape != length.shape:
+            raise ValueError("Both lists of indices and lengths must be the same length")
+        out = np.zeros(idx.size, dtype=np.uint32)
+        steps = _u64(0)
+        rc = load().nm_count_from_sequence(self._h, s.ctypes.data, s.size, idx.ctypes.data, length.ctypes.data,
+                                           idx.size, int(reverse_complement), out.ctypes.data, C.byref(steps))
+        if rc == NM_EARG:
+            if np.any(length == 0):
+                raise ValueError("All elements of the kmer list must have non-zero length")
+            raise IndexError("The sum of the index and length of each k-mer must be less than or equal to the "
+                             "length of the input byte sequence")
+        check(rc, "nm_count_from_sequence")
+        return (out, steps.value) if return_steps else out
+
+    def min_unique(self, seg, num_kmers: int, kmer_lengths, is_range: bool, initial_search_length: int = 0,
+                   use_rc: bool = True, algo: str = "auto", dtype=None):
+        """(array of num_kmers minimum unique lengths, Stats) for one segment buffer."""
+        s = as_u8(seg)
+        kl = _klist(kmer_lengths, is_range)
+        dt = np.dtype(dtype) if dtype is not None else out_dtype(int(max(kmer_lengths)))[0]
+        out = np.zeros(max(int(num_kmers), 1), dtype=dt)
+        st = Stats()
+        rc = load().nm_min_unique(self._h, s.ctypes.data, s.size, int(num_kmers),
+                                  NM_MODE_RANGE if is_range else NM_MODE_LIST, kl.ctypes.data, kl.size,
+                                  int(initial_search_length), int(use_rc), ALGOS[algo], dt.itemsize,
+                                  out.ctypes.data, C.byref(st))
+        if rc == NM_EARG:
+            raise ValueError("invalid search arguments (k-mer lengths must be positive, min <= max, "
+                             "initial search length inside the range, num_kmers <= segment length)")
+        check(rc, "nm_min_unique")
+        return out[:num_kmers], st
+
+
+def _klist(kmer_lengths, is_range: bool) -> np.ndarray:
+    if is_range:
+        return np.array([min(kmer_lengths), max(kmer_lengths)], dtype=np.uint32)
+    return np.ascontiguousarray(list(kmer_lengths), dtype=np.uint32)
+
+
+class Workspace:
+    """One CUDA stream + device scratch for segments up to max_seg_len (nm_workspace_*)."""
+
+    def __init__(self, index: Index, max_seg_len: int, cuda_stream: int | None = None):
+        self.index = index
+        h = _vp()
+        check(load().nm_workspace_create(index._h, int(max_seg_len), _vp(cuda_stream) if cuda_stream else None,
+                                         C.byref(h)), "nm_workspace_create")
+        self._h = h
+        self._keep = None
+
+    def close(self):
+        if getattr(self, "_h", None):
+            load().nm_workspace_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def upload(self, seg_ptr: int, seg_len: int):
+        check(load().nm_workspace_upload(self._h, seg_ptr, int(seg_len)), "nm_workspace_upload")
+
+    def search(self, num_kmers: int, kmer_lengths, is_range: bool, initial_search_length: int = 0,
+               use_rc: bool = True, algo: str = "auto", out_width: int = 1):
+        kl = _klist(kmer_lengths, is_range)
+        self._keep = kl
+        rc = load().nm_workspace_search(self._h, int(num_kmers), NM_MODE_RANGE if is_range else NM_MODE_LIST,
+                                        kl.ctypes.data, kl.size, int(initial_search_length), int(use_rc),
+                                        ALGOS[algo], int(out_width))
+        if rc == NM_EARG:
+            raise ValueError("invalid search arguments")
+        check(rc, "nm_workspace_search")
+
+    def download(self, out_ptr: int):
+        check(load().nm_workspace_download(self._h, out_ptr), "nm_workspace_download")
+
+    def sync(self) -> Stats:
+        st = Stats()
+        check(load().nm_workspace_sync(self._h, C.byref(st)), "nm_workspace_sync")
+        return st
+
+    def checksum(self) -> int:
+        v = _u64(0)
+        check(load().nm_workspace_checksum(self._h, C.byref(v)), "nm_workspace_checksum")
+        return v.value
+
+
+class PinnedBuffer:
+    """Page-locked host staging buffer exposed as a numpy uint8 array."""
+
+    def __init__(self, nbytes: int):
+        self.ptr = load().nm_host_alloc(int(nbytes))
+        if not self.ptr:
+            raise MemoryError("nm_host_alloc")
+        self.nbytes = int(nbytes)
+        self.array = np.ctypeslib.as_array((C.c_uint8 * self.nbytes).from_address(self.ptr))
+
+    def close(self):
+        if getattr(self, "ptr", None):
+            self.array = None
+            load().nm_host_free(self.ptr)
+            self.ptr = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def checksum_host(arr: np.ndarray) -> int:
+    """numpy twin of the device checksum (nm_core.cuh checksum_term), for device-resident runs."""
+    i = np.arange(1, arr.size + 1, dtype=np.uint64)
+    with np.errstate(over="ignore"):
+        h = (i * np.uint64(0x9E3779B97F4A7C15)) ^ (arr.astype(np.uint64) * np.uint64(0xC2B2AE3D27D4EB4F))
+        h ^= h >> np.uint64(29)
+        h *= np.uint64(0xBF58476D1CE4E5B9)
+        h ^= h >> np.uint64(32)
+        return int(h.sum(dtype=np.uint64))
+
+
+def probe_random_access(device: int, nbytes: int, granule: int, chains: int, steps: int):
+    rate, ms = C.c_double(0), C.c_float(0)
+    check(load().nm_probe_random_access(device, int(nbytes), granule, int(chains), steps, C.byref(rate), C.byref(ms)),
+          "nm_probe_random_access")
+    return rate.value, ms.value

@@ -1,0 +1,88 @@
+"""Drop-in for the reference's C extension `newmap._c_newmap_count_kmers` (src/newmap-count.c):
+same two functions, same argument meaning, same exception types -- backed by the CUDA library
+through ctypes, with the index kept resident in HBM between calls instead of being re-read from
+disk on every call (newmap-count.c:9-17,136)."""
+from __future__ import annotations
+
+import os
+import threading
+
+from . import _lib
+
+_cache: dict = {}
+_cache_lock = threading.Lock()
+
+
+def open_index(index_path, device: int | None = None) -> _lib.Index:
+    """Process-wide cache of resident indexes keyed by (real path, mtime, size, device)."""
+    if device is None:
+        device = int(os.environ.get("NEWMAP_B200_DEVICE", os.environ.get("LOCAL_RANK", "0")))
+    path = os.path.realpath(os.fspath(index_path))
+    try:
+        st = os.stat(path)
+    except OSError:
+        raise OSError("Could not load reference index from file\n")     # newmap-count.c:13-16
+    key = (path, st.st_mtime_ns, st.st_size, device)
+    with _cache_lock:
+        ix = _cache.get(key)
+        if ix is None or ix._h is None:
+            ix = _lib.Index(path, device)
+            _cache[key] = ix
+        return ix
+
+
+def close_all() -> None:
+    with _cache_lock:
+        for ix in _cache.values():
+            ix.close()
+        _cache.clear()
+
+
+def _check_threads(num_threads) -> None:
+    # the reference parses num_threads with the 'b' format (newmap-count.c:36,102): 0..255 or OverflowError.
+    # Accepted for interface compatibility and otherwise ignored on the GPU.
+    if not isinstance(num_threads, int) or isinstance(num_threads, bool) and False:
+        raise TypeError("an integer is required")
+    if not 0 <= num_threads <= 255:
+        raise OverflowError("unsigned byte integer is out of range")
+
+
+def count_kmers(index_path: str, kmers: list, num_threads: int = 1) -> list:
+    """newmap-count.c:28-89: occurrences of each byte-string k-mer in the index."""
+    _check_threads(num_threads)
+    if not isinstance(kmers, list):
+        raise TypeError("Second argument must be a list of kmer byte strings")
+    for k in kmers:
+        if not isinstance(k, bytes):
+            raise TypeError("All elements of the kmer list must be byte strings")
+        if len(k) == 0:
+            raise ValueError("All elements of the kmer list must have non-zero length")
+    ix = open_index(index_path)
+    lens = [len(k) for k in kmers]
+    offs, acc = [], 0
+    for n in lens:
+        offs.append(acc)
+        acc += n
+    return ix.count(b"".join(kmers), offs, lens).tolist()
+
+
+def count_kmers_from_sequence(index_path: str, sequence, indices: list, lengths: list, num_threads: int = 1) -> list:
+    """newmap-count.c:91-206: occurrences of sequence[i:i+l] for each (i, l)."""
+    _check_threads(num_threads)
+    if isinstance(sequence, str):
+        raise TypeError("a bytes-like object is required, not 'str'")
+    if not isinstance(indices, list):
+        raise TypeError("Third argument must be a list of integers")
+    if not isinstance(lengths, list):
+        raise TypeError("Fourth argument must be a list of integers")
+    if len(indices) != len(lengths):
+        raise ValueError("Both lists of indices and lengths must be the same length")
+    for i, n in zip(indices, lengths):
+        if not isinstance(i, int) or not isinstance(n, int):
+            raise TypeError("All elements of the the index and length lists must be integers")
+        if i < 0:
+            raise IndexError("All elements of the the index list must be non-negative integers")
+        if n < 0:
+            raise ValueError("All lengths in the length listlist must be non-negative integers")
+    ix = open_index(index_path)
+    return ix.count(sequence, indices, lengths).tolist()

@@ -1,0 +1,171 @@
+// nm_kernels.cu -- CUDA kernels (sm_100a) of the `newmap search` hot path.
+//
+// Pointer-chasing rank work: no tensor cores.  What matters here is (i) enough independent
+// searches in flight to cover HBM latency (one or two dependent chains per thread, blocks sized
+// for full occupancy, grids >> 148 SMs), (ii) one 32-byte sector per rank query on the rank32
+// layout, (iii) coalesced streaming of the segment arrays.  Per-thread bodies live in nm_core.cuh.
+#include "nm_kernels.cuh"
+
+namespace nm {
+
+namespace {
+
+constexpr int kBlock = 256;
+
+inline unsigned grid_for(uint64_t n, int block = kBlock) { return (unsigned)((n + block - 1) / block); }
+
+__device__ __forceinline__ void flush_counter(unsigned long long *ctr, uint32_t v) {
+  // warp-aggregate, one atomic per warp
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  if ((threadIdx.x & 31) == 0 && v) atomicAdd(ctr, (unsigned long long)v);
+}
+__device__ __forceinline__ void flush_counter64(unsigned long long *ctr, unsigned long long v) {
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  if ((threadIdx.x & 31) == 0 && v) atomicAdd(ctr, v);
+}
+
+__global__ void __launch_bounds__(kBlock) k_transcode(const uint8_t *native, uint64_t n_blocks, uint64_t bwt_len,
+                                                      uint32_t *rank32, uint64_t n64_total) {
+  const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < n64_total) transcode_thread(native, n_blocks, bwt_len, rank32, t);
+}
+
+__global__ void __launch_bounds__(kBlock) k_seed_transcode(const uint64_t *seed64, SeedEntry32 *seed32, uint64_t n) {
+  const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < n) seed_transcode_thread(seed64, seed32, t);
+}
+
+template <bool RC>
+__global__ void __launch_bounds__(kBlock) k_count(DevIndex ix, const uint8_t *seq, const uint64_t *idx,
+                                                  const uint64_t *len, uint64_t n, uint32_t *counts,
+                                                  unsigned long long *counters) {
+  const uint64_t q = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  uint32_t steps = 0;
+  if (q < n) counts[q] = count_one<RC>(ix, seq, idx[q], len[q], steps);
+  flush_counter(&counters[CTR_LF], steps);
+}
+
+__global__ void __launch_bounds__(kBlock) k_prep(DevIndex ix, SegParams P) {
+  const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p < P.seg_len) prep_thread(ix, P, p);
+}
+
+__global__ void __launch_bounds__(kBlock) k_nb_tile(SegParams P, uint32_t ntiles) {
+  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < ntiles) nb_tile_thread(P, t);
+}
+
+__global__ void __launch_bounds__(kBlock) k_trajectory(DevIndex ix, SegParams P) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  uint32_t steps = 0, nq = 0;
+  if (i < P.num_kmers) trajectory_thread(ix, P, i, steps, nq);
+  flush_counter(&P.counters[CTR_LF], steps);
+  flush_counter(&P.counters[CTR_QUERIES], nq);
+}
+
+__global__ void __launch_bounds__(kBlock) k_free_fast(DevIndex ix, SegParams P) {
+  const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+  uint32_t steps = 0;
+  if (p <= P.seg_len) free_fast_thread(ix, P, p, steps);
+  flush_counter(&P.counters[CTR_LF], steps);
+}
+
+__global__ void __launch_bounds__(kBlock) k_free_generic(DevIndex ix, SegParams P, bool all) {
+  const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+  uint32_t steps = 0, ns = 0;
+  if (p <= P.seg_len) free_generic_thread(ix, P, p, all, steps, ns);
+  flush_counter(&P.counters[CTR_LF], steps);
+  flush_counter(&P.counters[CTR_GENERIC], ns);
+}
+
+__global__ void __launch_bounds__(kBlock) k_resolve(DevIndex ix, SegParams P) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  uint64_t ref_lf = 0;
+  if (i < P.num_kmers) resolve_thread(ix, P, i, ref_lf);
+  if (P.want_ref_lf) flush_counter64(&P.counters[CTR_REF_LF], ref_lf);
+}
+
+__global__ void __launch_bounds__(kBlock) k_checksum(const void *out, int width, uint64_t n, unsigned long long *sum) {
+  unsigned long long acc = 0;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+    const uint32_t v = width == 1 ? ((const uint8_t *)out)[i] : width == 2 ? ((const uint16_t *)out)[i] : ((const uint32_t *)out)[i];
+    acc += checksum_term(i, v);
+  }
+  flush_counter64(sum, acc);
+}
+
+// random-access probe: every thread walks its own chain; the next offset depends on the loaded
+// data, so loads of one chain are serialised exactly like the LF steps of one search.
+template <int WORDS>  // 32-bit words per granule: 8, 16, 32
+__global__ void __launch_bounds__(kBlock) k_probe(const uint32_t *buf, uint64_t n_granules, uint64_t chains,
+                                                  uint32_t steps, unsigned long long *sink) {
+  const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= chains) return;
+  uint64_t x = t * 0x9E3779B97F4A7C15ull + 0x1234567ull;
+  uint32_t acc = 0;
+  for (uint32_t s = 0; s < steps; ++s) {
+    x ^= x >> 27; x *= 0x3C79AC492BA7B653ull; x ^= x >> 33; x *= 0x1C69B3F74AC4AE35ull; x ^= x >> 27;
+    const uint64_t g = x % n_granules;
+    const uint4 *p = reinterpret_cast<const uint4 *>(buf + g * WORDS);
+    uint32_t v = 0;
+#pragma unroll
+    for (int j = 0; j < WORDS / 4; ++j) {
+      const uint4 q = __ldg(p + j);
+      v += q.x ^ q.y ^ q.z ^ q.w;
+    }
+    acc += v;
+    x += v;  // data dependence
+  }
+  if (acc == 0x7fffffffu) atomicAdd(sink, 1ull);
+}
+
+}  // namespace
+
+void launch_transcode(const uint8_t *native, uint64_t n_blocks, uint64_t bwt_len, uint32_t *rank32,
+                      uint64_t n64_total, cudaStream_t st) {
+  k_transcode<<<grid_for(n64_total), kBlock, 0, st>>>(native, n_blocks, bwt_len, rank32, n64_total);
+}
+void launch_seed_transcode(const uint64_t *seed64, SeedEntry32 *seed32, uint64_t entries, cudaStream_t st) {
+  k_seed_transcode<<<grid_for(entries), kBlock, 0, st>>>(seed64, seed32, entries);
+}
+void launch_count(const DevIndex &ix, const uint8_t *seq, const uint64_t *idx, const uint64_t *len, uint64_t n,
+                  bool rc, uint32_t *counts, unsigned long long *counters, cudaStream_t st) {
+  if (n == 0) return;
+  if (rc) k_count<true><<<grid_for(n), kBlock, 0, st>>>(ix, seq, idx, len, n, counts, counters);
+  else k_count<false><<<grid_for(n), kBlock, 0, st>>>(ix, seq, idx, len, n, counts, counters);
+}
+void launch_prep(const DevIndex &ix, const SegParams &P, cudaStream_t st) {
+  if (P.seg_len == 0) return;
+  k_prep<<<grid_for(P.seg_len), kBlock, 0, st>>>(ix, P);
+  const uint32_t ntiles = (P.seg_len + kTile - 1) / kTile;
+  k_nb_tile<<<grid_for(ntiles), kBlock, 0, st>>>(P, ntiles);
+}
+void launch_trajectory(const DevIndex &ix, const SegParams &P, cudaStream_t st) {
+  if (P.num_kmers == 0) return;
+  k_trajectory<<<grid_for(P.num_kmers), kBlock, 0, st>>>(ix, P);
+}
+void launch_free_fast(const DevIndex &ix, const SegParams &P, cudaStream_t st) {
+  k_free_fast<<<grid_for((uint64_t)P.seg_len + 1), kBlock, 0, st>>>(ix, P);
+}
+void launch_free_generic(const DevIndex &ix, const SegParams &P, bool all, cudaStream_t st) {
+  k_free_generic<<<grid_for((uint64_t)P.seg_len + 1), kBlock, 0, st>>>(ix, P, all);
+}
+void launch_resolve(const DevIndex &ix, const SegParams &P, cudaStream_t st) {
+  if (P.num_kmers == 0) return;
+  k_resolve<<<grid_for(P.num_kmers), kBlock, 0, st>>>(ix, P);
+}
+void launch_checksum(const void *out, int out_width, uint64_t n, unsigned long long *sum, cudaStream_t st) {
+  if (n == 0) return;
+  unsigned g = grid_for(n);
+  if (g > 148 * 8) g = 148 * 8;
+  k_checksum<<<g, kBlock, 0, st>>>(out, out_width, n, sum);
+}
+void launch_probe(const uint8_t *buf, uint64_t n_granules, uint32_t granule, uint64_t chains, uint32_t steps,
+                  unsigned long long *sink, cudaStream_t st) {
+  const uint32_t *b = reinterpret_cast<const uint32_t *>(buf);
+  if (granule == 32) k_probe<8><<<grid_for(chains), kBlock, 0, st>>>(b, n_granules, chains, steps, sink);
+  else if (granule == 64) k_probe<16><<<grid_for(chains), kBlock, 0, st>>>(b, n_granules, chains, steps, sink);
+  else k_probe<32><<<grid_for(chains), kBlock, 0, st>>>(b, n_granules, chains, steps, sink);
+}
+
+}  // namespace nm

@@ -1,0 +1,23 @@
+// nm_kernels.cuh -- launch wrappers of the kernels in nm_kernels.cu (host-side declarations)
+#pragma once
+#include <cuda_runtime.h>
+
+#include "nm_core.cuh"
+
+namespace nm {
+
+void launch_transcode(const uint8_t *native, uint64_t n_blocks, uint64_t bwt_len, uint32_t *rank32,
+                      uint64_t n64_total, cudaStream_t st);
+void launch_seed_transcode(const uint64_t *seed64, SeedEntry32 *seed32, uint64_t entries, cudaStream_t st);
+void launch_count(const DevIndex &ix, const uint8_t *seq, const uint64_t *idx, const uint64_t *len, uint64_t n,
+                  bool rc, uint32_t *counts, unsigned long long *counters, cudaStream_t st);
+void launch_prep(const DevIndex &ix, const SegParams &P, cudaStream_t st);
+void launch_trajectory(const DevIndex &ix, const SegParams &P, cudaStream_t st);
+void launch_free_fast(const DevIndex &ix, const SegParams &P, cudaStream_t st);
+void launch_free_generic(const DevIndex &ix, const SegParams &P, bool all, cudaStream_t st);
+void launch_resolve(const DevIndex &ix, const SegParams &P, cudaStream_t st);
+void launch_checksum(const void *out, int out_width, uint64_t n, unsigned long long *sum, cudaStream_t st);
+void launch_probe(const uint8_t *buf, uint64_t n_granules, uint32_t granule, uint64_t chains, uint32_t steps,
+                  unsigned long long *sink, cudaStream_t st);
+
+}  // namespace nm

@@ -1,0 +1,618 @@
+// nm_lib.cu -- host side of libnewmap_b200.so: .awfmi loader, device-resident index, segment
+// workspaces and the C-ABI of include/newmap_b200.h.  No CPU fallback anywhere: every entry point
+// that computes launches the kernels of nm_kernels.cu or fails.
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/newmap_b200.h"
+#include "nm_kernels.cuh"
+
+namespace {
+
+thread_local std::string g_cuda_error;
+
+int cuda_fail(cudaError_t e, const char *what) {
+  g_cuda_error = std::string(what) + ": " + cudaGetErrorString(e);
+  return NM_ECUDA;
+}
+#define NM_CUDA(call)                                  \
+  do {                                                 \
+    cudaError_t e__ = (call);                          \
+    if (e__ != cudaSuccess) return cuda_fail(e__, #call); \
+  } while (0)
+
+}  // namespace
+
+struct nm_index {
+  nm::DevIndex dev{};
+  int device = 0;
+  uint64_t n_blocks = 0;
+  uint64_t seed_entries = 0;
+  uint32_t sa_ratio = 0;
+  bool has_rank32 = false;
+  uint64_t device_bytes = 0;
+  void *d_native = nullptr, *d_rank32 = nullptr, *d_seed32 = nullptr, *d_seed64 = nullptr;
+  nm_workspace *default_ws = nullptr;  // used by nm_min_unique
+  std::mutex mu;                       // serialises calls that share default_ws / count scratch
+};
+
+struct nm_workspace {
+  nm_index *ix = nullptr;
+  cudaStream_t stream = nullptr;
+  bool own_stream = false;
+  uint64_t max_seg_len = 0;
+  // device buffers
+  uint8_t *d_seg = nullptr, *d_codes = nullptr;
+  uint32_t *d_seedkey = nullptr, *d_nb = nullptr, *d_tile_first = nullptr, *d_G = nullptr, *d_R = nullptr;
+  void *d_out = nullptr;
+  uint32_t *d_klist = nullptr;
+  uint32_t klist_cap = 0;
+  unsigned long long *d_counters = nullptr;
+  unsigned long long *h_counters = nullptr;  // pinned
+  cudaEvent_t ev[8]{};
+  // last call
+  nm::SegParams P{};
+  uint64_t seg_len = 0;
+  bool have_search = false;
+  int algo_req = 0, algo_used = 0;
+  bool timed_h2d = false, timed_d2h = false;
+  void *pending_out = nullptr;
+};
+
+namespace {
+
+// AwFmFile.c:20-171 (writer) / :174-300 (reader): "AwFmIndex\n" | u32 version | u32 featureFlags |
+// u8 suffixArrayCompressionRatio | u8 kmerLengthInSeedTable | u8 alphabetType | u8 storeOriginalSequence |
+// u64 bwtLength | blocks | u64 prefixSums[6] | seed table | ...
+constexpr size_t kHeaderBytes = 30;
+
+int load_index(const char *path, int device, nm_index **out) {
+  int ndev = 0;
+  NM_CUDA(cudaGetDeviceCount(&ndev));
+  if (ndev <= 0) return cuda_fail(cudaErrorNoDevice, "cudaGetDeviceCount");
+  if (device < 0 || device >= ndev) return NM_EARG;
+  NM_CUDA(cudaSetDevice(device));
+
+  FILE *f = fopen(path, "rb");
+  if (!f) return NM_EOPEN;
+  struct Closer {
+    FILE *f;
+    ~Closer() { if (f) fclose(f); }
+  } closer{f};
+  uint8_t hdr[kHeaderBytes];
+  if (fread(hdr, 1, kHeaderBytes, f) != kHeaderBytes) return NM_ESHORT;
+  if (memcmp(hdr, "AwFmIndex\n", 10) != 0) return NM_EFORMAT;
+  uint32_t version;
+  memcpy(&version, hdr + 10, 4);
+  if (version != 8 || hdr[20] != 2) return NM_EVERSION;  // AwFmIndexStruct.c version, AwFmAlphabetDna = 2
+  uint64_t bwt_len;
+  memcpy(&bwt_len, hdr + 22, 8);
+  const uint32_t seed_len = hdr[19];
+  if (bwt_len == 0 || seed_len == 0 || seed_len > 15) return NM_EFORMAT;
+
+  nm_index *ix = new (std::nothrow) nm_index();
+  if (!ix) return NM_EALLOC;
+  struct Guard {
+    nm_index *ix;
+    ~Guard() { if (ix) nm_index_close(ix); }
+  } guard{ix};
+  ix->device = device;
+  ix->sa_ratio = hdr[18];
+  ix->n_blocks = 1 + (bwt_len - 1) / 256;  // AwFmIndexStruct.c:102-104
+  ix->seed_entries = 1ull << (2 * seed_len);
+  const uint64_t native_bytes = (ix->n_blocks + 1) * nm::kNativeBlockBytes;
+  const uint64_t seed_bytes = ix->seed_entries * 16;
+
+  // stage through pinned host memory in chunks so the file streams straight into HBM
+  const size_t chunk = 64u << 20;
+  uint8_t *stage = nullptr;
+  if (cudaHostAlloc((void **)&stage, chunk, cudaHostAllocDefault) != cudaSuccess) return NM_EALLOC;
+  struct StageFree {
+    uint8_t *p;
+    ~StageFree() { cudaFreeHost(p); }
+  } stage_free{stage};
+
+  if (cudaMalloc(&ix->d_native, native_bytes) != cudaSuccess) return NM_EALLOC;
+  if (cudaMalloc(&ix->d_seed64, seed_bytes) != cudaSuccess) return NM_EALLOC;
+  ix->device_bytes = native_bytes + seed_bytes;
+
+  auto stream_in = [&](void *dst, uint64_t bytes) -> int {
+    uint64_t done = 0;
+    while (done < bytes) {
+      const size_t want = (size_t)((bytes - done < chunk) ? bytes - done : chunk);
+      if (fread(stage, 1, want, f) != want) return NM_ESHORT;
+      if (cudaMemcpy((uint8_t *)dst + done, stage, want, cudaMemcpyHostToDevice) != cudaSuccess) return NM_ECUDA;
+      done += want;
+    }
+    return NM_OK;
+  };
+  int rc = stream_in(ix->d_native, ix->n_blocks * nm::kNativeBlockBytes);
+  if (rc != NM_OK) return rc;
+  uint64_t prefix[6];
+  if (fread(prefix, 8, 6, f) != 6) return NM_ESHORT;
+  if (prefix[5] != bwt_len || prefix[0] != 1) return NM_EFORMAT;
+  for (int l = 0; l < 5; ++l)
+    if (prefix[l] > prefix[l + 1]) return NM_EFORMAT;
+  rc = stream_in(ix->d_seed64, seed_bytes);
+  if (rc != NM_OK) return rc;
+
+  // pad block after the last one: zero planes, counters = totals, so that a rank at p == 256*n_blocks is defined
+  uint64_t pad[20];
+  memset(pad, 0, sizeof pad);
+  for (int l = 0; l < 5; ++l) pad[12 + l] = prefix[l + 1] - prefix[l];
+  pad[12 + 5] = 1;
+  NM_CUDA(cudaMemcpy((uint8_t *)ix->d_native + ix->n_blocks * nm::kNativeBlockBytes, pad, nm::kNativeBlockBytes,
+                     cudaMemcpyHostToDevice));
+
+  ix->dev.native = (const uint8_t *)ix->d_native;
+  ix->dev.seed64 = (const uint64_t *)ix->d_seed64;
+  for (int l = 0; l < 6; ++l) ix->dev.C[l] = prefix[l];
+  ix->dev.bwt_len = bwt_len;
+  ix->dev.seed_len = seed_len;
+
+  // derived layouts (device-side transcode of the unchanged file contents)
+  if (bwt_len < 0xFFFFFFFEull) {
+    const uint64_t n64 = (ix->n_blocks + 1) * 4;
+    if (cudaMalloc(&ix->d_rank32, n64 * nm::kRank32Words * 4) != cudaSuccess) return NM_EALLOC;
+    if (cudaMalloc(&ix->d_seed32, ix->seed_entries * sizeof(nm::SeedEntry32)) != cudaSuccess) return NM_EALLOC;
+    ix->device_bytes += n64 * nm::kRank32Words * 4 + ix->seed_entries * sizeof(nm::SeedEntry32);
+    nm::launch_transcode(ix->dev.native, ix->n_blocks, bwt_len, (uint32_t *)ix->d_rank32, n64, 0);
+    nm::launch_seed_transcode(ix->dev.seed64, (nm::SeedEntry32 *)ix->d_seed32, ix->seed_entries, 0);
+    NM_CUDA(cudaGetLastError());
+    NM_CUDA(cudaDeviceSynchronize());
+    ix->dev.rank32 = (const uint32_t *)ix->d_rank32;
+    ix->dev.seed32 = (const nm::SeedEntry32 *)ix->d_seed32;
+    ix->has_rank32 = true;
+  }
+  guard.ix = nullptr;
+  *out = ix;
+  return NM_OK;
+}
+
+int ws_alloc(nm_workspace *ws) {
+  const uint64_t n = ws->max_seg_len;
+  const uint64_t ntiles = (n + nm::kTile - 1) / nm::kTile + 1;
+  NM_CUDA(cudaMalloc((void **)&ws->d_seg, n + 16));
+  NM_CUDA(cudaMalloc((void **)&ws->d_codes, n + 16));
+  NM_CUDA(cudaMalloc((void **)&ws->d_seedkey, (n + 1) * 4));
+  NM_CUDA(cudaMalloc((void **)&ws->d_nb, (n + 1) * 4));
+  NM_CUDA(cudaMalloc((void **)&ws->d_tile_first, ntiles * 4));
+  NM_CUDA(cudaMalloc((void **)&ws->d_G, (n + 2) * 4));
+  NM_CUDA(cudaMalloc((void **)&ws->d_R, (n + 1) * 4));
+  NM_CUDA(cudaMalloc(&ws->d_out, (n + 1) * 4));
+  NM_CUDA(cudaMalloc((void **)&ws->d_counters, nm::CTR_N * 8));
+  NM_CUDA(cudaHostAlloc((void **)&ws->h_counters, nm::CTR_N * 8, cudaHostAllocDefault));
+  for (auto &e : ws->ev) NM_CUDA(cudaEventCreate(&e));
+  return NM_OK;
+}
+
+enum { EV_H2D0 = 0, EV_H2D1, EV_PREP1, EV_SEARCH1, EV_GENERIC1, EV_RESOLVE1, EV_D2H0, EV_D2H1 };
+
+// launches prep + the chosen algorithm on ws->stream; nothing is synchronised here
+int run_search(nm_workspace *ws, int algo) {
+  nm_index *ix = ws->ix;
+  nm::SegParams &P = ws->P;
+  cudaStream_t st = ws->stream;
+  static const unsigned long long init_counters[nm::CTR_N] = {0, 0, 0, 0, ~0ull, 0, 0, 0};
+  NM_CUDA(cudaMemcpyAsync(ws->d_counters, init_counters, sizeof init_counters, cudaMemcpyHostToDevice, st));
+  NM_CUDA(cudaEventRecord(ws->ev[EV_H2D1], st));
+  nm::launch_prep(ix->dev, P, st);
+  NM_CUDA(cudaEventRecord(ws->ev[EV_PREP1], st));
+  if (algo == NM_ALGO_TRAJECTORY) {
+    nm::launch_trajectory(ix->dev, P, st);
+    NM_CUDA(cudaEventRecord(ws->ev[EV_SEARCH1], st));
+    NM_CUDA(cudaEventRecord(ws->ev[EV_GENERIC1], st));
+    NM_CUDA(cudaEventRecord(ws->ev[EV_RESOLVE1], st));
+  } else {
+    const bool fast = (algo != NM_ALGO_FREE_GENERIC) && ix->has_rank32 && P.kmin >= ix->dev.seed_len;
+    P.fast = fast ? 1 : 0;
+    if (fast) nm::launch_free_fast(ix->dev, P, st);
+    NM_CUDA(cudaEventRecord(ws->ev[EV_SEARCH1], st));
+    nm::launch_free_generic(ix->dev, P, !fast, st);
+    NM_CUDA(cudaEventRecord(ws->ev[EV_GENERIC1], st));
+    nm::launch_resolve(ix->dev, P, st);
+    NM_CUDA(cudaEventRecord(ws->ev[EV_RESOLVE1], st));
+  }
+  NM_CUDA(cudaGetLastError());
+  NM_CUDA(cudaMemcpyAsync(ws->h_counters, ws->d_counters, nm::CTR_N * 8, cudaMemcpyDeviceToHost, st));
+  ws->algo_used = algo == NM_ALGO_AUTO ? NM_ALGO_AUTO : algo;
+  return NM_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int nm_abi_version(void) { return NM_ABI_VERSION; }
+
+const char *nm_strerror(int code) {
+  switch (code) {
+    case NM_OK: return "ok";
+    case NM_EOPEN: return "could not open the index file";
+    case NM_EFORMAT: return "not a valid .awfmi index";
+    case NM_EVERSION: return "unsupported .awfmi version or alphabet (need v8, DNA)";
+    case NM_EALLOC: return "allocation failed";
+    case NM_ESHORT: return "index file is truncated";
+    case NM_EARG: return "invalid argument";
+    case NM_ECUDA: return "CUDA error";
+    case NM_EUNSUPPORTED: return "unsupported";
+    default: return "unknown error";
+  }
+}
+
+const char *nm_last_cuda_error(void) { return g_cuda_error.c_str(); }
+
+int nm_device_count(void) {
+  int n = 0;
+  const cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess) return cuda_fail(e, "cudaGetDeviceCount");
+  return n;
+}
+
+int nm_index_open(const char *path, int device, nm_index **out) {
+  if (!path || !out) return NM_EARG;
+  *out = nullptr;
+  return load_index(path, device, out);
+}
+
+void nm_index_close(nm_index *ix) {
+  if (!ix) return;
+  cudaSetDevice(ix->device);
+  if (ix->default_ws) nm_workspace_destroy(ix->default_ws);
+  cudaFree(ix->d_native);
+  cudaFree(ix->d_rank32);
+  cudaFree(ix->d_seed32);
+  cudaFree(ix->d_seed64);
+  delete ix;
+}
+
+int nm_index_info_get(const nm_index *ix, nm_index_info *info) {
+  if (!ix || !info) return NM_EARG;
+  info->bwt_length = ix->dev.bwt_len;
+  info->n_blocks = ix->n_blocks;
+  for (int l = 0; l < 6; ++l) info->prefix_sums[l] = ix->dev.C[l];
+  info->device_bytes = ix->device_bytes;
+  info->seed_length = ix->dev.seed_len;
+  info->sa_compression_ratio = ix->sa_ratio;
+  info->has_rank32 = ix->has_rank32 ? 1u : 0u;
+  info->device = ix->device;
+  return NM_OK;
+}
+
+int nm_count_from_sequence(nm_index *ix, const uint8_t *seq, uint64_t seq_len, const uint64_t *idx,
+                           const uint64_t *len, uint64_t n, int reverse_complement, uint32_t *counts,
+                           uint64_t *lf_steps) {
+  if (!ix || (n && (!idx || !len || !counts)) || (seq_len && !seq)) return NM_EARG;
+  for (uint64_t q = 0; q < n; ++q)  // newmap-count.c:63-68,184-190
+    if (len[q] == 0 || idx[q] > seq_len || len[q] > seq_len - idx[q]) return NM_EARG;
+  if (n == 0) return NM_OK;
+  std::lock_guard<std::mutex> lock(ix->mu);
+  NM_CUDA(cudaSetDevice(ix->device));
+  uint8_t *d_seq = nullptr;
+  uint64_t *d_idx = nullptr, *d_len = nullptr;
+  uint32_t *d_counts = nullptr;
+  unsigned long long *d_ctr = nullptr;
+  int rc = NM_OK;
+  auto body = [&]() -> int {
+    NM_CUDA(cudaMalloc((void **)&d_seq, seq_len + 16));
+    NM_CUDA(cudaMalloc((void **)&d_idx, n * 8));
+    NM_CUDA(cudaMalloc((void **)&d_len, n * 8));
+    NM_CUDA(cudaMalloc((void **)&d_counts, n * 4));
+    NM_CUDA(cudaMalloc((void **)&d_ctr, nm::CTR_N * 8));
+    NM_CUDA(cudaMemset(d_ctr, 0, nm::CTR_N * 8));
+    NM_CUDA(cudaMemcpy(d_seq, seq, seq_len, cudaMemcpyHostToDevice));
+    NM_CUDA(cudaMemcpy(d_idx, idx, n * 8, cudaMemcpyHostToDevice));
+    NM_CUDA(cudaMemcpy(d_len, len, n * 8, cudaMemcpyHostToDevice));
+    nm::launch_count(ix->dev, d_seq, d_idx, d_len, n, reverse_complement != 0, d_counts, d_ctr, 0);
+    NM_CUDA(cudaGetLastError());
+    NM_CUDA(cudaMemcpy(counts, d_counts, n * 4, cudaMemcpyDeviceToHost));
+    if (lf_steps) {
+      unsigned long long v = 0;
+      NM_CUDA(cudaMemcpy(&v, d_ctr + nm::CTR_LF, 8, cudaMemcpyDeviceToHost));
+      *lf_steps += v;
+    }
+    return NM_OK;
+  };
+  rc = body();
+  cudaFree(d_seq);
+  cudaFree(d_idx);
+  cudaFree(d_len);
+  cudaFree(d_counts);
+  cudaFree(d_ctr);
+  return rc;
+}
+
+int nm_workspace_create(nm_index *ix, uint64_t max_seg_len, void *cuda_stream, nm_workspace **out) {
+  if (!ix || !out || max_seg_len == 0 || max_seg_len >= 0xFFFFFF00ull) return NM_EARG;
+  *out = nullptr;
+  NM_CUDA(cudaSetDevice(ix->device));
+  nm_workspace *ws = new (std::nothrow) nm_workspace();
+  if (!ws) return NM_EALLOC;
+  ws->ix = ix;
+  ws->max_seg_len = max_seg_len;
+  if (cuda_stream) {
+    ws->stream = (cudaStream_t)cuda_stream;
+  } else {
+    if (cudaStreamCreateWithFlags(&ws->stream, cudaStreamNonBlocking) != cudaSuccess) {
+      delete ws;
+      return NM_ECUDA;
+    }
+    ws->own_stream = true;
+  }
+  const int rc = ws_alloc(ws);
+  if (rc != NM_OK) {
+    nm_workspace_destroy(ws);
+    return rc;
+  }
+  *out = ws;
+  return NM_OK;
+}
+
+void nm_workspace_destroy(nm_workspace *ws) {
+  if (!ws) return;
+  cudaSetDevice(ws->ix->device);
+  cudaStreamSynchronize(ws->stream);
+  cudaFree(ws->d_seg);
+  cudaFree(ws->d_codes);
+  cudaFree(ws->d_seedkey);
+  cudaFree(ws->d_nb);
+  cudaFree(ws->d_tile_first);
+  cudaFree(ws->d_G);
+  cudaFree(ws->d_R);
+  cudaFree(ws->d_out);
+  cudaFree(ws->d_klist);
+  cudaFree(ws->d_counters);
+  if (ws->h_counters) cudaFreeHost(ws->h_counters);
+  for (auto &e : ws->ev)
+    if (e) cudaEventDestroy(e);
+  if (ws->own_stream) cudaStreamDestroy(ws->stream);
+  delete ws;
+}
+
+int nm_workspace_upload(nm_workspace *ws, const uint8_t *seg, uint64_t seg_len) {
+  if (!ws || (seg_len && !seg) || seg_len > ws->max_seg_len) return NM_EARG;
+  NM_CUDA(cudaSetDevice(ws->ix->device));
+  NM_CUDA(cudaEventRecord(ws->ev[EV_H2D0], ws->stream));
+  if (seg_len) NM_CUDA(cudaMemcpyAsync(ws->d_seg, seg, seg_len, cudaMemcpyHostToDevice, ws->stream));
+  ws->seg_len = seg_len;
+  ws->timed_h2d = true;
+  ws->have_search = false;
+  return NM_OK;
+}
+
+int nm_workspace_search(nm_workspace *ws, uint64_t num_kmers, int mode, const uint32_t *klist, uint32_t nk,
+                        uint32_t initial_search_length, int use_rc, int algo, int out_width) {
+  if (!ws || !klist || nk == 0) return NM_EARG;
+  if (num_kmers > ws->seg_len) return NM_EARG;
+  if (out_width != 1 && out_width != 2 && out_width != 4) return NM_EARG;
+  if (algo != NM_ALGO_AUTO && algo != NM_ALGO_TRAJECTORY && algo != NM_ALGO_FREE_GENERIC) return NM_EARG;
+  uint32_t kmin, kmax;
+  if (mode == NM_MODE_RANGE) {
+    if (nk != 2) return NM_EARG;
+    kmin = klist[0];
+    kmax = klist[1];
+    if (kmin == 0 || kmin > kmax) return NM_EARG;
+    // the reference never terminates when the first query is clamped below the lower bound
+    if (initial_search_length && initial_search_length < kmin) return NM_EARG;
+  } else if (mode == NM_MODE_LIST) {
+    kmin = kmax = klist[0];
+    for (uint32_t j = 0; j < nk; ++j) {
+      if (klist[j] == 0) return NM_EARG;
+      if (klist[j] < kmin) kmin = klist[j];
+      if (klist[j] > kmax) kmax = klist[j];
+    }
+    if (initial_search_length) return NM_EARG;  // search.py:137-140
+  } else {
+    return NM_EARG;
+  }
+  if (kmax >= 0xFFFFFFF0u) return NM_EARG;
+  if ((out_width == 1 && kmax > 0xFF) || (out_width == 2 && kmax > 0xFFFF)) return NM_EARG;
+  NM_CUDA(cudaSetDevice(ws->ix->device));
+  if (!ws->timed_h2d) NM_CUDA(cudaEventRecord(ws->ev[EV_H2D0], ws->stream));
+  if (mode == NM_MODE_LIST) {
+    if (nk > ws->klist_cap) {
+      NM_CUDA(cudaStreamSynchronize(ws->stream));
+      cudaFree(ws->d_klist);
+      ws->d_klist = nullptr;
+      NM_CUDA(cudaMalloc((void **)&ws->d_klist, (size_t)nk * 4));
+      ws->klist_cap = nk;
+    }
+    NM_CUDA(cudaMemcpyAsync(ws->d_klist, klist, (size_t)nk * 4, cudaMemcpyHostToDevice, ws->stream));
+  }
+  nm::SegParams &P = ws->P;
+  P.seg = ws->d_seg;
+  P.codes = ws->d_codes;
+  P.seedkey = ws->d_seedkey;
+  P.nb = ws->d_nb;
+  P.tile_first = ws->d_tile_first;
+  P.G = ws->d_G;
+  P.R = ws->d_R;
+  P.out = ws->d_out;
+  P.klist = ws->d_klist;
+  P.counters = ws->d_counters;
+  P.seg_len = (uint32_t)ws->seg_len;
+  P.num_kmers = (uint32_t)num_kmers;
+  P.kmin = kmin;
+  P.kmax = kmax;
+  P.nk = nk;
+  P.initial = initial_search_length;
+  P.mode = mode;
+  P.use_rc = use_rc ? 1 : 0;
+  P.out_width = out_width;
+  P.fast = 0;
+  P.want_ref_lf = 1;
+  ws->algo_req = algo;
+  ws->have_search = true;
+  ws->timed_d2h = false;
+  ws->pending_out = nullptr;
+  return run_search(ws, algo);
+}
+
+int nm_workspace_download(nm_workspace *ws, void *out) {
+  if (!ws || !ws->have_search || (!out && ws->P.num_kmers)) return NM_EARG;
+  NM_CUDA(cudaSetDevice(ws->ix->device));
+  NM_CUDA(cudaEventRecord(ws->ev[EV_D2H0], ws->stream));
+  if (ws->P.num_kmers)
+    NM_CUDA(cudaMemcpyAsync(out, ws->d_out, (size_t)ws->P.num_kmers * ws->P.out_width, cudaMemcpyDeviceToHost,
+                            ws->stream));
+  NM_CUDA(cudaEventRecord(ws->ev[EV_D2H1], ws->stream));
+  ws->timed_d2h = true;
+  ws->pending_out = out;
+  return NM_OK;
+}
+
+int nm_workspace_sync(nm_workspace *ws, nm_stats *stats) {
+  if (!ws) return NM_EARG;
+  NM_CUDA(cudaSetDevice(ws->ix->device));
+  NM_CUDA(cudaStreamSynchronize(ws->stream));
+  if (!ws->have_search) return NM_OK;
+  bool replayed = false;
+  float ms[7] = {0, 0, 0, 0, 0, 0, 0};
+  auto el = [&](int a, int b, float &dst) { cudaEventElapsedTime(&dst, ws->ev[a], ws->ev[b]); };
+  if (ws->timed_h2d) el(EV_H2D0, EV_H2D1, ms[0]);
+  el(EV_H2D1, EV_PREP1, ms[1]);
+  el(EV_PREP1, EV_SEARCH1, ms[2]);
+  el(EV_SEARCH1, EV_GENERIC1, ms[3]);
+  el(EV_GENERIC1, EV_RESOLVE1, ms[4]);
+  if (ws->timed_d2h) el(EV_D2H0, EV_D2H1, ms[5]);
+  if (ws->timed_d2h) el(EV_H2D0, EV_D2H1, ms[6]); else el(EV_H2D0, EV_RESOLVE1, ms[6]);
+  unsigned long long free_lf = ws->h_counters[nm::CTR_LF];
+  if (ws->algo_req == NM_ALGO_AUTO && ws->h_counters[nm::CTR_ANOMALY]) {
+    // A substring of the segment is absent from the index (sequence / index mismatch).  The
+    // reference reports the first zero count on ITS query trajectory: replay that trajectory.
+    void *out = ws->pending_out;
+    const bool d2h = ws->timed_d2h;
+    int rc = run_search(ws, NM_ALGO_TRAJECTORY);
+    if (rc != NM_OK) return rc;
+    if (d2h && ws->P.num_kmers)
+      NM_CUDA(cudaMemcpyAsync(out, ws->d_out, (size_t)ws->P.num_kmers * ws->P.out_width, cudaMemcpyDeviceToHost,
+                              ws->stream));
+    NM_CUDA(cudaStreamSynchronize(ws->stream));
+    replayed = true;
+  }
+  ws->timed_h2d = false;
+  if (stats) {
+    memset(stats, 0, sizeof *stats);
+    stats->positions = ws->P.num_kmers;
+    stats->lf_steps = ws->h_counters[nm::CTR_LF] + (replayed ? free_lf : 0);
+    stats->queries = ws->h_counters[nm::CTR_QUERIES];
+    stats->generic_searches = ws->h_counters[nm::CTR_GENERIC];
+    stats->ref_lf_steps = ws->h_counters[nm::CTR_REF_LF];
+    const unsigned long long key = ws->h_counters[nm::CTR_ZERO_KEY];
+    stats->zero_pos = -1;
+    stats->zero_len = 0;
+    stats->zero_round = -1;
+    if (key != ~0ull) {
+      stats->zero_pos = (int64_t)(key & 0xFFFFFFFFull);
+      stats->zero_round = (int64_t)(key >> 32);
+      uint32_t zl = 0;
+      NM_CUDA(cudaMemcpy(&zl, ws->d_G + stats->zero_pos, 4, cudaMemcpyDeviceToHost));
+      stats->zero_len = zl;
+    }
+    stats->algo_used = replayed ? NM_ALGO_TRAJECTORY : (uint32_t)ws->algo_req;
+    stats->replayed = replayed ? 1u : 0u;
+    stats->ms_h2d = ms[0];
+    stats->ms_prep = ms[1];
+    stats->ms_search = ms[2];
+    stats->ms_generic = ms[3];
+    stats->ms_resolve = ms[4];
+    stats->ms_d2h = ms[5];
+    stats->ms_total = ms[6];
+  }
+  return NM_OK;
+}
+
+int nm_workspace_checksum(nm_workspace *ws, uint64_t *sum) {
+  if (!ws || !sum || !ws->have_search) return NM_EARG;
+  NM_CUDA(cudaSetDevice(ws->ix->device));
+  unsigned long long *d = nullptr;
+  NM_CUDA(cudaMalloc((void **)&d, 8));
+  cudaMemsetAsync(d, 0, 8, ws->stream);
+  nm::launch_checksum(ws->d_out, ws->P.out_width, ws->P.num_kmers, d, ws->stream);
+  unsigned long long v = 0;
+  cudaError_t e = cudaMemcpyAsync(&v, d, 8, cudaMemcpyDeviceToHost, ws->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(ws->stream);
+  cudaFree(d);
+  if (e != cudaSuccess) return cuda_fail(e, "checksum");
+  *sum = v;
+  return NM_OK;
+}
+
+int nm_min_unique(nm_index *ix, const uint8_t *seg, uint64_t seg_len, uint64_t num_kmers, int mode,
+                  const uint32_t *klist, uint32_t nk, uint32_t initial_search_length, int use_rc, int algo,
+                  int out_width, void *out, nm_stats *stats) {
+  if (!ix) return NM_EARG;
+  if (seg_len == 0 || num_kmers == 0) {
+    if (stats) { memset(stats, 0, sizeof *stats); stats->zero_pos = -1; stats->zero_round = -1; }
+    return num_kmers == 0 ? NM_OK : NM_EARG;
+  }
+  std::lock_guard<std::mutex> lock(ix->mu);
+  if (!ix->default_ws || ix->default_ws->max_seg_len < seg_len) {
+    if (ix->default_ws) nm_workspace_destroy(ix->default_ws);
+    ix->default_ws = nullptr;
+    uint64_t cap = seg_len < (1u << 20) ? (1u << 20) : seg_len + seg_len / 8;
+    if (cap >= 0xFFFFFF00ull) cap = seg_len;
+    const int rc = nm_workspace_create(ix, cap, nullptr, &ix->default_ws);
+    if (rc != NM_OK) return rc;
+  }
+  nm_workspace *ws = ix->default_ws;
+  int rc = nm_workspace_upload(ws, seg, seg_len);
+  if (rc == NM_OK) rc = nm_workspace_search(ws, num_kmers, mode, klist, nk, initial_search_length, use_rc, algo, out_width);
+  if (rc == NM_OK) rc = nm_workspace_download(ws, out);
+  if (rc == NM_OK) rc = nm_workspace_sync(ws, stats);
+  return rc;
+}
+
+void *nm_host_alloc(uint64_t bytes) {
+  void *p = nullptr;
+  if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocDefault) != cudaSuccess) return nullptr;
+  return p;
+}
+void nm_host_free(void *p) {
+  if (p) cudaFreeHost(p);
+}
+
+int nm_probe_random_access(int device, uint64_t bytes, uint32_t granule, uint64_t chains, uint32_t steps,
+                           double *loads_per_second, float *ms_out) {
+  if ((granule != 32 && granule != 64 && granule != 128) || bytes < granule || !chains || !steps) return NM_EARG;
+  NM_CUDA(cudaSetDevice(device));
+  uint8_t *buf = nullptr;
+  unsigned long long *sink = nullptr;
+  cudaEvent_t a = nullptr, b = nullptr;
+  auto body = [&]() -> int {
+    NM_CUDA(cudaMalloc((void **)&buf, bytes));
+    NM_CUDA(cudaMalloc((void **)&sink, 8));
+    NM_CUDA(cudaMemset(buf, 0x5a, bytes));
+    NM_CUDA(cudaMemset(sink, 0, 8));
+    NM_CUDA(cudaEventCreate(&a));
+    NM_CUDA(cudaEventCreate(&b));
+    const uint64_t ng = bytes / granule;
+    nm::launch_probe(buf, ng, granule, chains, steps < 4 ? steps : 4, sink, 0);  // warm-up
+    NM_CUDA(cudaDeviceSynchronize());
+    NM_CUDA(cudaEventRecord(a, 0));
+    nm::launch_probe(buf, ng, granule, chains, steps, sink, 0);
+    NM_CUDA(cudaEventRecord(b, 0));
+    NM_CUDA(cudaEventSynchronize(b));
+    NM_CUDA(cudaGetLastError());
+    float ms = 0;
+    NM_CUDA(cudaEventElapsedTime(&ms, a, b));
+    if (ms_out) *ms_out = ms;
+    if (loads_per_second) *loads_per_second = (double)chains * steps / (ms * 1e-3);
+    return NM_OK;
+  };
+  const int rc = body();
+  if (a) cudaEventDestroy(a);
+  if (b) cudaEventDestroy(b);
+  cudaFree(buf);
+  cudaFree(sink);
+  return rc;
+}
+
+}  // extern "C"

@@ -1,0 +1,59 @@
+"""`newmap search` command line, flag-for-flag the reference's (newmap/main.py:89-188), on the
+B200 path.  `python -m newmap_b200 search genome.fa genome.awfmi -r 20:200 -o out/`."""
+from __future__ import annotations
+
+import sys
+from argparse import ArgumentParser
+
+from . import __version__, search
+from .util import INDEX_EXTENSION
+
+DEFAULT_KMER_BATCH_SIZE = 10000000
+DEFAULT_THREAD_COUNT = 1
+DEFAULT_KMER_SEARCH_RANGE = "20:200"
+FASTA_FILE_METAVAR = "fasta_file"
+
+
+def build_parser() -> ArgumentParser:
+    parser = ArgumentParser(prog="newmap", description="Newmap (B200): shortest unique sequence length at each "
+                                                       "position of a reference sequence")
+    parser.add_argument("--version", action="version", version=f"%(prog)s-b200 {__version__}")
+    sub = parser.add_subparsers(metavar="", required=True)
+    p = sub.add_parser("search", help="Find the shortest unique sequence length at each position in sequences")
+    p.set_defaults(func=search.main)
+    p.add_argument("fasta_file", metavar=FASTA_FILE_METAVAR, help="(gzipped) fasta file for kmer generation")
+    p.add_argument("index_file", nargs="?",
+                   help=f"reference index file to count occurances in (default: basename of {FASTA_FILE_METAVAR} "
+                        f"with the {INDEX_EXTENSION} extension)")
+    g = p.add_argument_group("output arguments")
+    g.add_argument("--search-range", "-r", metavar="RANGE", default=DEFAULT_KMER_SEARCH_RANGE,
+                   help="comma separated list of increasing lengths, or an inclusive range a:b "
+                        f"(default: {DEFAULT_KMER_SEARCH_RANGE})")
+    g.add_argument("--output-directory", "-o", metavar="DIR", default=".")
+    g.add_argument("--include-sequences", "-i", metavar="IDS")
+    g.add_argument("--exclude-sequences", "-x", metavar="IDS")
+    g.add_argument("--norc", action="store_true", help="do not search the reverse-complement strand")
+    g.add_argument("--verbose", "-v", action="store_true")
+    q = p.add_argument_group("performance arguments")
+    q.add_argument("--initial-search-length", "-l", type=int, metavar="LENGTH", default=0)
+    q.add_argument("--kmer-batch-size", "-s", default=DEFAULT_KMER_BATCH_SIZE, metavar="SIZE", type=int)
+    q.add_argument("--num-threads", "-t", default=DEFAULT_THREAD_COUNT, metavar="NUM", type=int,
+                   help="accepted for compatibility; ignored on the GPU")
+    q.add_argument("--device", type=int, default=None, help="CUDA device (default: $NEWMAP_B200_DEVICE or 0)")
+    q.add_argument("--algorithm", choices=["auto", "trajectory", "free_generic"], default="auto",
+                   help="auto: trajectory-free kernels (same bytes as the reference); trajectory: replay the "
+                        "reference's binary / linear search on the GPU")
+    return parser
+
+
+def parse_subcommands(argv=None):
+    args = build_parser().parse_args(argv)
+    args.func(args)
+
+
+def main():
+    parse_subcommands(sys.argv[1:])
+
+
+if __name__ == "__main__":
+    main()

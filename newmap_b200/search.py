@@ -1,0 +1,333 @@
+"""`newmap search` host driver on the B200 path.
+
+Same public surface as the reference's newmap/search.py -- SearchConfig (fields, from_args),
+write_unique_counts, binary_search, linear_search, get_kmer_counts, get_num_kmers,
+get_ambiguous_sequence_mask, update_upper_search_bound -- and the same outputs
+(<outdir>/<id>.unique.uint8|16|32, raw little-endian, one value per base), but the per-position
+search no longer lives in numpy + a count extension: each segment buffer is handed to
+libnewmap_b200.so (nm_workspace_* through ctypes), which computes the minimum unique length of
+every position on the GPU.  Segments are pipelined over a few workspaces so that host->device
+copies, kernels and device->host copies of consecutive segments overlap.  `num_threads` is
+accepted and ignored.  There is no CPU fallback.
+"""
+from __future__ import annotations
+
+import os
+from collections import deque
+from contextlib import ExitStack
+from dataclasses import dataclass, field
+from functools import partial
+from math import ceil, log2
+from pathlib import Path
+from typing import Callable
+
+import numpy as np
+
+from . import _lib
+from .count import open_index
+from .fasta import SequenceSegment, sequence_segments
+from .util import INDEX_EXTENSION, optional_gzip_open, verbose_print
+
+KMER_RANGE_SEPARATOR = ":"
+SEQUENCE_ID_SEPARATOR = ","
+INDEX_FILE_SEPARATOR = ","
+FASTA_FILE_SEPARATOR = ","
+
+COMPLEMENT_TRANSLATE_TABLE = bytes.maketrans(b"ACGTacgt", b"TGCAtgca")
+ALLOWED_BASES = b"ACGTactg"          # sic (search.py:23): the set is right, the order is not
+UNIQUE_COUNT_FILENAME_FORMAT = "{}.unique.{}"
+PIPELINE_DEPTH = int(os.environ.get("NEWMAP_B200_PIPELINE", "3"))
+
+
+def nil_search_log(*_: str):
+    pass
+
+
+@dataclass(frozen=True)
+class SearchConfig:
+    """Field-for-field the reference's SearchConfig (search.py:32-63); `device` and `algorithm`
+    are additions with neutral defaults."""
+    fasta_filepaths: list
+    fmindex_filepaths: list
+    kmer_lengths: list
+    is_binary_search: bool
+    use_reverse_complement: bool = True
+    output_directory: Path = field(default_factory=Path.cwd)
+    include_sequence_ids: list = field(default_factory=list)
+    exclude_sequence_ids: list = field(default_factory=list)
+    num_threads: int = 1                 # accepted, ignored on the GPU
+    kmer_batch_size: int = 1000000
+    initial_search_length: int = 0
+    verbose: bool = False
+    device: int | None = None            # CUDA device (default: $NEWMAP_B200_DEVICE, $LOCAL_RANK, 0)
+    algorithm: str = "auto"              # "auto" | "trajectory" | "free_generic" (include/newmap_b200.h)
+    log: Callable[..., None] = field(init=False, repr=False, compare=False)
+
+    def __post_init__(self):
+        object.__setattr__(self, "log", partial(verbose_print, True) if self.verbose else nil_search_log)
+
+    @classmethod
+    def from_args(cls, args):
+        """argparse namespace of `newmap search` -> SearchConfig (search.py:65-184)."""
+        output_directory = Path(args.output_directory) if args.output_directory else Path(".")
+        output_directory.mkdir(parents=True, exist_ok=True)
+        fasta_filenames = [Path(p) for p in args.fasta_file.split(FASTA_FILE_SEPARATOR)]
+        if not args.index_file:
+            index_filenames = [Path(Path(fasta_filenames[0]).stem + "." + INDEX_EXTENSION)]
+        else:
+            index_filenames = [Path(p) for p in args.index_file.split(INDEX_FILE_SEPARATOR)]
+        for index_filename in index_filenames:
+            if not index_filename.is_file():
+                raise FileNotFoundError(f"Index file not found: {index_filename}")
+        spec = args.search_range
+        if KMER_RANGE_SEPARATOR in spec:
+            try:
+                lo, hi = map(int, spec.split(KMER_RANGE_SEPARATOR))
+            except ValueError:
+                raise ValueError("Could not parse k-mer search range format")
+            if lo > hi:
+                raise ValueError("K-mer range start length is larger than the end length")
+            kmer_lengths, binary = list(range(lo, hi + 1)), True
+        else:
+            kmer_lengths, binary = list(map(int, spec.split(","))), False
+        if args.initial_search_length and not binary:
+            raise ValueError("Initial search length only valid when a range of k-mer lengths is given")
+        if args.include_sequences and args.exclude_sequences:
+            raise ValueError("Cannot specify both include and exclude sequences")
+        include = [s.encode() for s in args.include_sequences.split(SEQUENCE_ID_SEPARATOR)] \
+            if args.include_sequences else []
+        exclude = [s.encode() for s in args.exclude_sequences.split(SEQUENCE_ID_SEPARATOR)] \
+            if args.exclude_sequences else []
+        return cls(fasta_filepaths=fasta_filenames, fmindex_filepaths=index_filenames,
+                   kmer_lengths=kmer_lengths, is_binary_search=binary,
+                   use_reverse_complement=not args.norc, output_directory=output_directory,
+                   include_sequence_ids=include, exclude_sequence_ids=exclude, verbose=args.verbose,
+                   num_threads=args.num_threads, kmer_batch_size=args.kmer_batch_size,
+                   initial_search_length=args.initial_search_length,
+                   device=getattr(args, "device", None), algorithm=getattr(args, "algorithm", "auto"))
+
+
+# ------------------------------------------------------------------------------------------------
+# helpers with the reference's names
+# ------------------------------------------------------------------------------------------------
+def get_num_kmers(sequence_segment: SequenceSegment, max_kmer_length: int) -> int:
+    """search.py:727-741."""
+    n = len(sequence_segment.data)
+    return n if sequence_segment.epilogue else n - (max_kmer_length - 1)
+
+
+def get_ambiguous_sequence_mask(sequence_segment: SequenceSegment, num_positions: int) -> np.ndarray:
+    """True where the start byte is not one of b'ACGTacgt' (search.py:744-766)."""
+    buf = np.frombuffer(sequence_segment.data, dtype=np.uint8, count=num_positions)
+    lut = np.ones(256, dtype=bool)
+    lut[list(ALLOWED_BASES)] = False
+    return lut[buf]
+
+
+def update_upper_search_bound(upper_search_bound: np.ndarray, ambiguity_mask: np.ndarray,
+                              max_search_length: int, sequence_buffer_length: int) -> None:
+    """In-place upper k bound per position (search.py:769-871), in closed form: distance to the
+    next ambiguous start position, else to the end of the buffer, capped at max_search_length;
+    entries at ambiguous positions are left untouched.  (The GPU path computes the same quantity
+    in nm_core.cuh length_limit(); this host twin exists for API parity and tests.)"""
+    n = ambiguity_mask.size
+    assert sequence_buffer_length - n < max_search_length, \
+        "Excess sequence buffer length is greater than the maximum search length"
+    if n == 0:
+        return
+    pos = np.arange(n, dtype=np.int64)
+    nxt = np.where(ambiguity_mask, pos, np.int64(sequence_buffer_length))
+    nxt = np.minimum.accumulate(nxt[::-1])[::-1]          # next ambiguous position at or after i
+    room = np.minimum(nxt - pos, max_search_length)
+    keep = ~ambiguity_mask
+    upper_search_bound[keep] = room[keep].astype(upper_search_bound.dtype)
+
+
+def _raise_zero_count(segment_data: bytes, st: _lib.Stats):
+    """search.py:699-722."""
+    p, n = int(st.zero_pos), int(st.zero_len)
+    kmer = bytes(segment_data[p:p + n]).decode("utf-8")
+    raise RuntimeError(f"The following generated k-mer was not found in the index:\n{kmer}\n"
+                       f"Possibly a mismatch between the sequence and the index.")
+
+
+def _single(config: SearchConfig):
+    if len(config.fmindex_filepaths) != 1:
+        raise NotImplementedError("newmap_b200: simultaneous search over several index files is not built yet "
+                                  "(SURVEY.md §8(f) N3)")
+    return open_index(config.fmindex_filepaths[0], config.device)
+
+
+def get_kmer_counts(config: SearchConfig, sequences: list, sequence_indices: list, kmer_lengths: list) -> np.ndarray:
+    """Two-strand u32 counts of sequences[0][i:i+k] (search.py:647-724) on the GPU."""
+    if len(sequences) != 1:
+        raise NotImplementedError("newmap_b200: one sequence per call (SURVEY.md §8(f) N3)")
+    ix = _single(config)
+    seq = sequences[0]
+    total = ix.count(seq, sequence_indices, kmer_lengths)
+    if config.use_reverse_complement:
+        total = total + ix.count(seq, sequence_indices, kmer_lengths, reverse_complement=True)
+    zero = np.nonzero(total == 0)[0]
+    if zero.size:
+        i, k = sequence_indices[int(zero[0])], kmer_lengths[int(zero[0])]
+        raise RuntimeError(f"The following generated k-mer was not found in the index:\n"
+                           f"{bytes(seq[i:i + k]).decode('utf-8')}\n"
+                           f"Possibly a mismatch between the sequence and the index.")
+    return total
+
+
+def _search_segment(config: SearchConfig, sequence_segments_: tuple, data_type) -> tuple:
+    if len(sequence_segments_) != 1:
+        raise NotImplementedError("newmap_b200: one FASTA per search (SURVEY.md §8(f) N3)")
+    seg = sequence_segments_[0]
+    max_k = max(config.kmer_lengths)
+    num_kmers = get_num_kmers(seg, max_k)
+    ix = _single(config)
+    out, st = ix.min_unique(seg.data, num_kmers, config.kmer_lengths, config.is_binary_search,
+                            config.initial_search_length, config.use_reverse_complement, config.algorithm,
+                            dtype=data_type)
+    if st.zero_pos >= 0:
+        _raise_zero_count(seg.data, st)
+    ambiguous = int(get_ambiguous_sequence_mask(seg, num_kmers).sum())
+    return out, ambiguous
+
+
+def binary_search(config: SearchConfig, sequence_segments: tuple, min_kmer_length: int, max_kmer_length: int,
+                  data_type) -> tuple:
+    """(unique_lengths, ambiguous_positions_skipped) for one segment, range mode (search.py:383-548)."""
+    assert min_kmer_length == min(config.kmer_lengths) and max_kmer_length == max(config.kmer_lengths)
+    return _search_segment(config, sequence_segments, data_type)
+
+
+def linear_search(config: SearchConfig, sequence_segments: tuple, num_kmers: int, data_type) -> tuple:
+    """(unique_lengths, ambiguous_positions_skipped) for one segment, list mode (search.py:551-644)."""
+    return _search_segment(config, sequence_segments, data_type)
+
+
+# ------------------------------------------------------------------------------------------------
+# the pipelined driver
+# ------------------------------------------------------------------------------------------------
+class _Slot:
+    """One in-flight segment: pinned staging for input and output + a workspace (stream)."""
+
+    def __init__(self, ix: _lib.Index, max_seg_len: int, out_itemsize: int):
+        self.ws = _lib.Workspace(ix, max_seg_len)
+        self.inp = _lib.PinnedBuffer(max_seg_len)
+        self.out = _lib.PinnedBuffer(max_seg_len * out_itemsize)
+        self.job = None
+
+    def close(self):
+        self.ws.close()
+        self.inp.close()
+        self.out.close()
+
+
+def write_unique_counts(config: SearchConfig):
+    """FASTA -> <id>.unique.uintN, one value per base (search.py:197-380)."""
+    max_kmer_length = max(config.kmer_lengths)
+    min_kmer_length = min(config.kmer_lengths)
+    data_type, unique_count_suffix = _lib.out_dtype(max_kmer_length)
+    if len(config.fasta_filepaths) != 1 or len(config.fmindex_filepaths) != 1:
+        raise NotImplementedError("newmap_b200: simultaneous search over several FASTA / index files is not "
+                                  "built yet (SURVEY.md §8(f) N3)")
+    if config.is_binary_search and max_kmer_length > min_kmer_length:
+        config.log("Max {} iterations over range {}-{}".format(
+            ceil(log2(max_kmer_length - min_kmer_length) + 1), min_kmer_length, max_kmer_length))
+
+    ix = open_index(config.fmindex_filepaths[0], config.device)
+    lookahead_length = max_kmer_length - 1
+    requested_sequence_length = config.kmer_batch_size + lookahead_length
+    slots: list[_Slot] = []
+    inflight: deque = deque()
+    totals = dict(ambiguous=0, unique=0, none=0, max_len=min_kmer_length, min_len=max_kmer_length)
+    sequence_processed = False
+    current_sequence_id = b""
+    current_file = None
+
+    def finish(slot: _Slot):
+        seg, num_kmers, fh = slot.job
+        st = slot.ws.sync()
+        if st.zero_pos >= 0:
+            _raise_zero_count(seg.data, st)
+        res = slot.out.array[:num_kmers * data_type.itemsize].view(data_type)
+        if config.verbose:
+            ambiguous = int(get_ambiguous_sequence_mask(seg, num_kmers).sum())
+            unique = int(np.count_nonzero(res))
+            totals["ambiguous"] += ambiguous
+            totals["unique"] += unique
+            totals["none"] += num_kmers - unique - ambiguous
+            if unique:
+                totals["max_len"] = max(totals["max_len"], int(res.max()))
+                totals["min_len"] = min(totals["min_len"], int(res[res != 0].min()))
+            else:
+                config.log("No unique lengths found for this sequence segment")
+        res.tofile(fh)
+        slot.job = None
+
+    def drain():
+        while inflight:
+            finish(inflight.popleft())
+
+    with ExitStack() as stack:
+        fasta_file = stack.enter_context(optional_gzip_open(config.fasta_filepaths[0], "rb"))
+        stack.callback(lambda: [s.close() for s in slots])
+        for segment in sequence_segments(fasta_file, requested_sequence_length, lookahead_length):
+            if current_sequence_id != segment.id:
+                # include / exclude filter, evaluated exactly like search.py:268-278 -- including its
+                # quirk that with only --exclude-sequences given every sequence is skipped
+                if config.include_sequence_ids or config.exclude_sequence_ids:
+                    if (segment.id not in config.include_sequence_ids) or (segment.id in config.exclude_sequence_ids):
+                        continue
+                drain()
+                sequence_processed = True
+                print_summary_statisitcs(config, current_sequence_id, totals["unique"], totals["ambiguous"],
+                                         totals["none"], totals["max_len"], totals["min_len"])
+                current_sequence_id = segment.id
+                path = config.output_directory / UNIQUE_COUNT_FILENAME_FORMAT.format(
+                    segment.id.decode(), unique_count_suffix)
+                if current_file is not None:
+                    current_file.close()
+                current_file = stack.enter_context(open(path, "wb"))   # truncates, then appended per segment
+                config.log("Writing unique lengths for sequence ID: {}".format(segment.id.decode()))
+            num_kmers = get_num_kmers(segment, max_kmer_length)
+            config.log("Processing {} k-mers".format(num_kmers))
+            if len(inflight) >= PIPELINE_DEPTH:
+                finish(inflight.popleft())
+            slot = next((s for s in slots if s.job is None), None)
+            if slot is None:
+                slot = _Slot(ix, requested_sequence_length, data_type.itemsize)
+                slots.append(slot)
+            n = len(segment.data)
+            slot.inp.array[:n] = np.frombuffer(segment.data, dtype=np.uint8)
+            slot.job = (segment, num_kmers, current_file)
+            slot.ws.upload(slot.inp.ptr, n)
+            slot.ws.search(num_kmers, config.kmer_lengths, config.is_binary_search, config.initial_search_length,
+                           config.use_reverse_complement, config.algorithm, data_type.itemsize)
+            slot.ws.download(slot.out.ptr)
+            inflight.append(slot)
+        drain()
+        print_summary_statisitcs(config, current_sequence_id, totals["unique"], totals["ambiguous"],
+                                 totals["none"], totals["max_len"], totals["min_len"])
+    if not sequence_processed:
+        if config.include_sequence_ids:
+            raise ValueError(f"None of the included sequences were found: {config.include_sequence_ids}")
+        elif config.exclude_sequence_ids:
+            raise ValueError("The excluded sequences were too strict and nothing was processed: "
+                             f"{config.exclude_sequence_ids}")
+
+
+def print_summary_statisitcs(config, sequence_id, total_unique_lengths_count, total_ambiguous_positions,
+                             total_no_unique_lengths_count, max_length_found, min_length_found):
+    """search.py:885-902 (name kept, typo included)."""
+    if total_unique_lengths_count:
+        config.log(f"Finished writing unique lengths for sequence ID: {sequence_id.decode()}")
+        config.log(f"{total_unique_lengths_count} unique lengths found")
+        config.log(f"{total_ambiguous_positions} positions skipped due to ambiguity")
+        config.log(f"{total_no_unique_lengths_count} positions with no unique length found")
+        config.log(f"{max_length_found}-mer maximum unique length found")
+        config.log(f"{min_length_found}-mer minimum unique length found")
+
+
+def main(args):
+    config = SearchConfig.from_args(args)
+    write_unique_counts(config)

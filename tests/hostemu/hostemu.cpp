@@ -1,0 +1,116 @@
+// tests/hostemu/hostemu.cpp -- TEST INFRASTRUCTURE ONLY.
+// Compiles the per-thread kernel bodies of newmap_b200/csrc/nm_core.cuh with the host compiler
+// and runs them serially (thread id = loop index) in the same order nm_lib.cu launches them, so
+// the algorithmic logic of the CUDA path can be checked against the oracle in the build
+// container, which has no GPU.  The product never loads this library.
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+#include "../../newmap_b200/csrc/nm_core.cuh"
+
+using namespace nm;
+
+struct EmuIndex {
+  std::vector<uint8_t> native;
+  std::vector<uint32_t> rank32;
+  std::vector<SeedEntry32> seed32;
+  std::vector<uint64_t> seed64;
+  DevIndex dev{};
+  bool has_rank32 = false;
+};
+
+extern "C" {
+
+EmuIndex *emu_index_open(const char *path) {
+  FILE *f = fopen(path, "rb");
+  if (!f) return nullptr;
+  uint8_t hdr[30];
+  if (fread(hdr, 1, 30, f) != 30) { fclose(f); return nullptr; }
+  uint64_t bwt_len;
+  memcpy(&bwt_len, hdr + 22, 8);
+  const uint32_t sl = hdr[19];
+  EmuIndex *ix = new EmuIndex();
+  const uint64_t nb = 1 + (bwt_len - 1) / 256;
+  ix->native.assign((nb + 1) * 160, 0);
+  if (fread(ix->native.data(), 160, nb, f) != nb) { fclose(f); delete ix; return nullptr; }
+  uint64_t prefix[6];
+  if (fread(prefix, 8, 6, f) != 6) { fclose(f); delete ix; return nullptr; }
+  const uint64_t entries = 1ull << (2 * sl);
+  ix->seed64.resize(entries * 2);
+  if (fread(ix->seed64.data(), 16, entries, f) != entries) { fclose(f); delete ix; return nullptr; }
+  fclose(f);
+  uint64_t *pad = reinterpret_cast<uint64_t *>(ix->native.data() + nb * 160);
+  for (int l = 0; l < 5; ++l) pad[12 + l] = prefix[l + 1] - prefix[l];
+  pad[17] = 1;
+  ix->dev.native = ix->native.data();
+  ix->dev.seed64 = ix->seed64.data();
+  for (int l = 0; l < 6; ++l) ix->dev.C[l] = prefix[l];
+  ix->dev.bwt_len = bwt_len;
+  ix->dev.seed_len = sl;
+  const uint64_t n64 = (nb + 1) * 4;
+  ix->rank32.resize(n64 * 8);
+  for (uint64_t t = 0; t < n64; ++t) transcode_thread(ix->native.data(), nb, bwt_len, ix->rank32.data(), t);
+  ix->seed32.resize(entries);
+  for (uint64_t t = 0; t < entries; ++t) seed_transcode_thread(ix->seed64.data(), ix->seed32.data(), t);
+  ix->dev.rank32 = ix->rank32.data();
+  ix->dev.seed32 = ix->seed32.data();
+  ix->has_rank32 = true;
+  return ix;
+}
+
+void emu_index_close(EmuIndex *ix) { delete ix; }
+
+int emu_count(EmuIndex *ix, const uint8_t *seq, uint64_t seq_len, const uint64_t *idx, const uint64_t *len,
+              uint64_t n, int rc, uint32_t *counts, uint64_t *lf) {
+  uint32_t steps = 0;
+  for (uint64_t q = 0; q < n; ++q) {
+    if (len[q] == 0 || idx[q] + len[q] > seq_len) return -6;
+    counts[q] = rc ? count_one<true>(ix->dev, seq, idx[q], len[q], steps) : count_one<false>(ix->dev, seq, idx[q], len[q], steps);
+  }
+  if (lf) *lf += steps;
+  return 0;
+}
+
+// stats: [0] lf, [1] queries, [2] generic searches, [3] anomaly, [4] zero pos (-1), [5] zero len, [6] zero round, [7] ref lf
+int emu_min_unique(EmuIndex *ix, const uint8_t *seg, uint32_t seg_len, uint32_t num_kmers, int mode,
+                   const uint32_t *klist, uint32_t nk, uint32_t initial, int use_rc, int algo, int out_width,
+                   void *out, int64_t *stats) {
+  std::vector<uint8_t> codes(seg_len + 16);
+  std::vector<uint32_t> seedkey(seg_len + 1), nb(seg_len + 1), tf((seg_len + kTile - 1) / kTile + 1), G(seg_len + 2), R(seg_len + 1);
+  unsigned long long ctr[CTR_N] = {0, 0, 0, 0, ~0ull, 0, 0, 0};
+  SegParams P{};
+  P.seg = seg; P.codes = codes.data(); P.seedkey = seedkey.data(); P.nb = nb.data(); P.tile_first = tf.data();
+  P.G = G.data(); P.R = R.data(); P.out = out; P.klist = klist; P.counters = ctr;
+  P.seg_len = seg_len; P.num_kmers = num_kmers; P.nk = nk; P.initial = initial; P.mode = mode;
+  P.use_rc = use_rc; P.out_width = out_width; P.want_ref_lf = 1;
+  if (mode == 0) { P.kmin = klist[0]; P.kmax = klist[1]; }
+  else { P.kmin = P.kmax = klist[0]; for (uint32_t j = 0; j < nk; ++j) { if (klist[j] < P.kmin) P.kmin = klist[j]; if (klist[j] > P.kmax) P.kmax = klist[j]; } }
+  for (uint32_t p = 0; p < seg_len; ++p) prep_thread(ix->dev, P, p);
+  const uint32_t ntiles = (seg_len + kTile - 1) / kTile;
+  for (uint32_t t = 0; t < ntiles; ++t) nb_tile_thread(P, t);
+  uint32_t steps = 0, nq = 0, ns = 0;
+  uint64_t ref_lf = 0;
+  if (algo == 1) {
+    for (uint32_t i = 0; i < num_kmers; ++i) trajectory_thread(ix->dev, P, i, steps, nq);
+  } else {
+    const bool fast = (algo != 2) && ix->has_rank32 && P.kmin >= ix->dev.seed_len;
+    P.fast = fast;
+    if (fast) for (uint32_t p = 0; p <= seg_len; ++p) free_fast_thread(ix->dev, P, p, steps);
+    for (uint32_t p = 0; p <= seg_len; ++p) free_generic_thread(ix->dev, P, p, !fast, steps, ns);
+    for (uint32_t i = 0; i < num_kmers; ++i) resolve_thread(ix->dev, P, i, ref_lf);
+  }
+  if (stats) {
+    stats[0] = steps; stats[1] = nq; stats[2] = ns; stats[3] = (int64_t)ctr[CTR_ANOMALY];
+    stats[4] = -1; stats[5] = 0; stats[6] = -1; stats[7] = (int64_t)ref_lf;
+    if (ctr[CTR_ZERO_KEY] != ~0ull) {
+      stats[4] = (int64_t)(ctr[CTR_ZERO_KEY] & 0xFFFFFFFFull);
+      stats[6] = (int64_t)(ctr[CTR_ZERO_KEY] >> 32);
+      stats[5] = G[stats[4]];
+    }
+  }
+  return 0;
+}
+
+}  // extern "C"

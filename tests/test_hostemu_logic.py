@@ -1,0 +1,119 @@
+"""CPU-side check of the CUDA path's LOGIC: the per-thread kernel bodies (nm_core.cuh) compiled
+for the host and run serially (tests/hostemu) against the oracle and the reference-made golden
+fixtures.  The same comparisons run on the real kernels in tests/test_gpu_parity.py."""
+import numpy as np
+import pytest
+
+from conftest import GOLD, run_klist
+from hostemu import EmuIndex
+from oracle import ora
+
+ALGOS = {"auto": 0, "trajectory": 1, "free_generic": 2}
+
+
+def _segments(run):
+    max_k = run["k"][1] if run["range"] else max(run["k"])
+    for seg in ora.segments(GOLD / run["fasta"], run["batch"], max_k - 1):
+        n = len(seg.data) if seg.epilogue else len(seg.data) - (max_k - 1)
+        yield seg, n
+
+
+@pytest.mark.parametrize("algo", list(ALGOS))
+def test_golden_searches(manifest, golden_searches, algo):
+    cache = {}
+    for run in manifest["searches"]:
+        ix = cache.setdefault(run["index"], EmuIndex(GOLD / f"{run['index']}.awfmi"))
+        klist = run_klist(run)
+        got = {}
+        for seg, n in _segments(run):
+            out, stats = ix.min_unique_segment(seg.data, n, klist, run["range"], run.get("initial", 0),
+                                               not run.get("norc", False), ALGOS[algo])
+            assert stats[3] == 0 and stats[4] == -1, (run["id"], stats)
+            got.setdefault(seg.id, []).append(out)
+        for sid, parts in got.items():
+            want = golden_searches[f"run{run['id']}|{sid.decode()}"]
+            arr = np.concatenate(parts)
+            bad = np.nonzero(arr != want)[0]
+            assert bad.size == 0, (algo, run, sid, bad[:10], arr[bad[:10]], want[bad[:10]])
+
+
+def test_golden_counts(manifest, golden_counts):
+    for c in manifest["counts"]:
+        ix = EmuIndex(GOLD / f"{c['index']}.awfmi")
+        o = ora.OracleIndex(GOLD / f"{c['index']}.awfmi")
+        seq = dict(ora.fasta_records(GOLD / c["fasta"]))[c["sequence"].encode()]
+        idx, ln = golden_counts[c["key"] + "|idx"], golden_counts[c["key"] + "|len"]
+        got, lf = ix.count(seq, idx, ln)
+        assert np.array_equal(got, golden_counts[c["key"] + "|count"])
+        o.lf_steps = 0
+        assert np.array_equal(ix.count(seq, idx, ln, rc=True)[0], o.count(seq, idx, ln, rc=True))
+
+
+def test_trajectory_lf_steps_and_zero_event_match_oracle():
+    ix = EmuIndex(GOLD / "quirk_s4.awfmi")
+    o = ora.OracleIndex(GOLD / "quirk_s4.awfmi")
+    seq = dict(ora.fasta_records(GOLD / "quirk.fa"))[b"chr1"]
+    seg = seq[:1199]
+    o.lf_steps = o.queries = 0
+    want = o.min_unique_segment(seg, 1000, list(range(20, 201)), True, nthreads=1)
+    out, stats = ix.min_unique_segment(seg, 1000, list(range(20, 201)), True, algo=1)
+    assert np.array_equal(out, want)
+    assert stats[0] == o.lf_steps and stats[1] == o.queries
+    # a sequence that is not in the index: same first zero-count k-mer as the oracle reports
+    rng = np.random.default_rng(1)
+    alien = bytes(np.frombuffer(b"ACGT", dtype=np.uint8)[rng.integers(0, 4, 600)])
+    with pytest.raises(ora.ZeroCount) as e:
+        o.min_unique_segment(alien, 500, list(range(20, 101)), True, nthreads=1)
+    for algo in (0, 1):
+        out, stats = ix.min_unique_segment(alien, 500, list(range(20, 101)), True, algo=algo)
+        if algo == 0:
+            assert stats[3] == 1     # the trajectory-free search flags the anomaly; nm_lib.cu then replays
+        else:
+            p, ln = int(stats[4]), int(stats[5])
+            assert ora.zero_count_message(alien[p:p + ln].decode()) == str(e.value)
+
+
+def test_ref_lf_estimate_matches_trajectory_on_clean_sequence():
+    """stats.ref_lf_steps (LF steps of the reference's trajectory, derived from the thresholds) equals
+    the steps the trajectory kernel really executes when no query contains an ambiguous base."""
+    ix = EmuIndex(GOLD / "quirk_s4.awfmi")
+    seq = dict(ora.fasta_records(GOLD / "quirk.fa"))[b"chr2"]
+    seg = seq[0:2400 + 39]      # no N inside (first N of chr2 is at 2511)
+    assert b"N" not in seg
+    kl = list(range(8, 41))
+    _, st_t = ix.min_unique_segment(seg, 2400, kl, True, algo=1)
+    _, st_f = ix.min_unique_segment(seg, 2400, kl, True, algo=0)
+    assert st_f[7] == st_t[0]
+
+
+def test_random_small_genomes_all_algorithms_agree_with_oracle(tmp_path):
+    if not ora.ref_available():
+        pytest.skip("needs oracle/_ref to build fresh indexes")
+    rng = np.random.default_rng(2024)
+    for trial in range(6):
+        n1, n2 = int(rng.integers(200, 3000)), int(rng.integers(50, 800))
+        alphabet = np.frombuffer(b"ACGT" if trial % 2 else b"ACGTacgtNNn", dtype=np.uint8)
+        recs = []
+        for name, n in (("s1", n1), ("s2", n2)):
+            a = alphabet[rng.integers(0, alphabet.size, n)].copy()
+            if n > 300:   # plant repeats so that long k-mers stay non-unique
+                a[n // 2:n // 2 + 120] = a[10:130]
+            recs.append((name, a))
+        fa = tmp_path / f"t{trial}.fa"
+        with open(fa, "wb") as fh:
+            for name, a in recs:
+                fh.write(b">" + name.encode() + b"\n" + a.tobytes() + b"\n")
+        seed = int(rng.integers(1, 7))
+        ixp = tmp_path / f"t{trial}.awfmi"
+        ora.ref_build_index(fa, ixp, 8, seed)
+        o, e = ora.OracleIndex(ixp), EmuIndex(ixp)
+        for klist, is_range in ((list(range(3, 40)), True), (list(range(seed, 70)), True), ([5, 9, 17, 40], False),
+                                ([30, 12, 12, 50], False)):
+            batch = int(rng.integers(20, 500))
+            max_k = max(klist)
+            for seg in ora.segments(fa, batch, max_k - 1):
+                n = len(seg.data) if seg.epilogue else len(seg.data) - (max_k - 1)
+                want = o.min_unique_segment(seg.data, n, klist, is_range, nthreads=1)
+                for algo in (0, 1, 2):
+                    got, st = e.min_unique_segment(seg.data, n, klist, is_range, algo=algo)
+                    assert np.array_equal(got, want), (trial, klist[:3], is_range, algo, batch)

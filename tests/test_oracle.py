@@ -189,3 +189,23 @@ def test_zero_count_raises_like_reference():
     with pytest.raises(ora.ZeroCount) as e:
         o.min_unique_segment(b"ACGTTTGCATGCAAGT", 16, list(range(3, 6)), True)
     assert "was not found in the index" in str(e.value)
+
+
+@pytest.mark.skipif(not ora.ref_available(), reason="needs oracle/_ref")
+def test_refdrive_matches_oracle_and_goldens(manifest, golden_searches):
+    """The CPU-baseline driver (reference C code + restated host loop) gives the reference's bytes."""
+    from oracle import refdrive
+    for run in manifest["searches"]:
+        if run["id"] % 4:       # a quarter of the runs is plenty: each round re-reads the index like the reference
+            continue
+        klist = run_klist(run)
+        max_k = max(klist)
+        got = {}
+        for seg in ora.segments(GOLD / run["fasta"], run["batch"], max_k - 1):
+            n = len(seg.data) if seg.epilogue else len(seg.data) - (max_k - 1)
+            out = refdrive.search_segment(GOLD / f"{run['index']}.awfmi", seg.data, n, klist, run["range"],
+                                          run.get("initial", 0), not run.get("norc", False), 2)
+            got.setdefault(seg.id, []).append(out)
+        for sid, parts in got.items():
+            want = golden_searches[f"run{run['id']}|{sid.decode()}"]
+            assert np.array_equal(np.concatenate(parts).astype(want.dtype), want), (run["id"], sid)

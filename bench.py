@@ -349,7 +349,7 @@ def main():
         # random 32 B-sector probe on this GPU, same run (2 GiB buffer, 8 M chains x 64 dependent loads)
         probe = {}
         for g in (32, 64, 128):
-            rate, _ = _lib.probe_random_access(local, 2 << 30, g, 8 << 20, 64)
+            rate, _ = _lib.probe_random_access(local, 2 << 30, g, 2 << 20, 64, 4)
             probe[g] = rate
         achieved = lf * 64 / (ms_search * 1e-3) / 1e9 if ms_search else None
         line = dict(base)
@@ -370,7 +370,7 @@ def main():
                          "lf_steps_per_position": lf / max(1, positions_per_step * args.steps),
                          "ref_trajectory_lf_steps_per_position": ref_lf / max(1, positions_per_step * args.steps),
                          "random_sector_probe": {"loads_per_s": probe, "gbs_32B": probe[32] * 32 / 1e9,
-                                                 "how": "2 GiB buffer, 8 Mi chains x 64 dependent loads"},
+                                                 "how": "2 GiB buffer, 2 Mi threads x 4 chains x 64 dependent loads"},
                          "frac_random_sector": (lf * 2 / (ms_search * 1e-3) / probe[32]) if ms_search else None},
             "kernel_ms": {k: sum(s[k] for s in stats) / max(1, launches) for k in
                           ("ms_prep", "ms_search", "ms_generic", "ms_resolve")},

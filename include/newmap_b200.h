@@ -124,11 +124,11 @@ int nm_workspace_checksum(nm_workspace *ws, uint64_t *sum);
 void *nm_host_alloc(uint64_t bytes);
 void nm_host_free(void *p);
 
-/* Random-access roofline probe: `chains` independent dependent-load chains of `steps` loads of
- * `granule` bytes (32, 64 or 128, granule-aligned) at pseudo-random offsets of a `bytes`-sized
- * device buffer.  Returns loads/second measured with CUDA events. */
+/* Random-access roofline probe: `chains` threads each walk `mlp` (1, 2 or 4) independent chains of
+ * `steps` dependent loads of `granule` bytes (32, 64 or 128, granule-aligned) at pseudo-random
+ * offsets of a `bytes`-sized (power of two) device buffer.  Returns loads/second (CUDA events). */
 int nm_probe_random_access(int device, uint64_t bytes, uint32_t granule, uint64_t chains, uint32_t steps,
-                           double *loads_per_second, float *ms);
+                           uint32_t mlp, double *loads_per_second, float *ms);
 
 #ifdef __cplusplus
 }

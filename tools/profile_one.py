@@ -1,0 +1,27 @@
+"""Short single-GPU program for ncu: a few searches of one 10 M-position segment of a bench
+workload (default c2_100m).  `python tools/profile_one.py [workload] [repeats] [algo]`."""
+import sys
+from pathlib import Path
+
+import numpy as np
+
+sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+import bench  # noqa: E402
+from newmap_b200 import _lib  # noqa: E402
+
+workload = sys.argv[1] if len(sys.argv) > 1 else "c2_100m"
+repeats = int(sys.argv[2]) if len(sys.argv) > 2 else 3
+algo = sys.argv[3] if len(sys.argv) > 3 else "auto"
+fa, ixp = bench.prepare_workload(workload)
+(segs, total) = bench.load_segments(fa, 1, 1)
+seg, n = segs[0]
+ix = _lib.Index(ixp, device=0)
+ws = _lib.Workspace(ix, len(seg.data))
+pb = _lib.PinnedBuffer(len(seg.data))
+pb.array[:] = np.frombuffer(seg.data, dtype=np.uint8)
+ws.upload(pb.ptr, len(seg.data))
+kl = list(range(20, 201))
+for _ in range(repeats):
+    ws.search(n, kl, True, algo=algo, out_width=1)
+    st = ws.sync()
+print({k: v for k, v in st.as_dict().items() if k.startswith("ms_") or k.endswith("steps") or k == "generic_searches"})

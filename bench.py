@@ -360,7 +360,7 @@ def main():
                     "h2d_bytes_per_step": int(sum(len(s.data) for s, _ in segs)),
                     "d2h_bytes_per_step": int(positions_per_step), "ms_per_step": ms_e2e / args.steps,
                     "timing": "host clock bracketed by device synchronize; 3 pipelined workspaces"},
-            "gpu_launches": 5 * launches,
+            "gpu_launches": 6 * launches,
             "clocks": clocks.summary(),
             "roofline": {"bound": "hbm", "kernel": "k_free_fast", "achieved": achieved, "peak": hbm_peak,
                          "unit": "GB/s", "frac": (achieved / hbm_peak) if achieved else None, "peak_source": peak_src,

@@ -104,6 +104,7 @@ constexpr uint8_t kNoStart = 0x20;     // search.py:23,744-766: start byte not i
 constexpr uint32_t kNone = 0u;               // G: no unique suffix within bounds
 constexpr uint32_t kInf = 0xFFFFFFFFu;       // R: other strand still present at the longest length
 constexpr uint32_t kPending = 0xFFFFFFFEu;   // G/R: to be computed by the generic kernel
+constexpr uint32_t kDeep = 0xFFFFFFFDu;      // G/R: undecided at the depth cap of the first pass
 constexpr uint32_t kSeedInvalid = 0xFFFFFFFFu;
 constexpr uint32_t kNoBarrier = 0xFFFFFFFFu;
 constexpr uint32_t kTile = 64;               // nb[] tile (positions per thread of nb_tile_thread)
@@ -120,6 +121,7 @@ struct DevIndex {
   const uint32_t *rank32;     // (n64 + 1) * 8 u32, or nullptr
   const SeedEntry32 *seed32;  // 4^seed_len entries, or nullptr
   const uint64_t *seed64;     // 4^seed_len {start,end} pairs exactly as in the file
+  const uint32_t *c32;        // prefixSums as u32[6] in device memory (rank32 path), or nullptr
   uint64_t C[6];              // prefixSums, AwFmCreate.c:299-305
   uint64_t bwt_len;
   uint32_t seed_len;
@@ -190,18 +192,69 @@ NM_HD void lf_native(const DevIndex &ix, Range64 &r, unsigned letter) {
 // ---------------------------------------------------------------------------------------------
 // rank on the derived 32-byte layout (a,c,g,t only; bwt_len < 2^32-1)
 // block = { u32 count[4] | u64 plane0 | u64 plane1 }, code = plane1<<1 | plane0, 64 positions.
-// A block that holds an x or $ symbol carries kPoison in all four counts.
+// A block that holds an x or $ symbol carries kPoison in all four counts.  One block = one 32-byte
+// DRAM sector, fetched with a single 256-bit load (LDG.E.256 on sm_100a).
 // ---------------------------------------------------------------------------------------------
-NM_HD uint32_t occ_rank32(const uint32_t *rank32, unsigned letter, uint32_t p, bool &poison) {
-  const uint32_t *w = rank32 + (size_t)(p >> 6) * kRank32Words;
-  const uint32_t c = ld32(w + letter);
-  const u32x4 pl = ld128(w + 4);
-  const uint64_t p0 = (uint64_t)pl.x | ((uint64_t)pl.y << 32);
-  const uint64_t p1 = (uint64_t)pl.z | ((uint64_t)pl.w << 32);
-  const uint64_t m = ((letter & 1u) ? p0 : ~p0) & ((letter & 2u) ? p1 : ~p1);
-  const uint64_t mask = (1ull << (p & 63u)) - 1ull;
-  poison = poison || (c == kPoison);
-  return c + (uint32_t)popc64(m & mask);
+struct Rank32Block {
+  uint32_t c[4];
+  uint64_t p0, p1;
+};
+
+NM_HD Rank32Block ld_rank32(const uint32_t *rank32, uint32_t blk) {
+  const uint32_t *w = rank32 + (size_t)blk * kRank32Words;
+  Rank32Block r;
+#if defined(__CUDA_ARCH__)
+  uint32_t v4, v5, v6, v7;
+  asm volatile("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+               : "=r"(r.c[0]), "=r"(r.c[1]), "=r"(r.c[2]), "=r"(r.c[3]), "=r"(v4), "=r"(v5), "=r"(v6), "=r"(v7)
+               : "l"(w));
+  r.p0 = (uint64_t)v4 | ((uint64_t)v5 << 32);
+  r.p1 = (uint64_t)v6 | ((uint64_t)v7 << 32);
+#else
+  for (int l = 0; l < 4; ++l) r.c[l] = w[l];
+  r.p0 = (uint64_t)w[4] | ((uint64_t)w[5] << 32);
+  r.p1 = (uint64_t)w[6] | ((uint64_t)w[7] << 32);
+#endif
+  return r;
+}
+
+NM_HD uint32_t sel4(unsigned letter, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  return letter == 0 ? a : letter == 1 ? b : letter == 2 ? c : d;
+}
+
+NM_HD uint32_t occ_in_block(const Rank32Block &b, unsigned letter, uint32_t off) {
+  const uint64_t m = ((letter & 1u) ? b.p0 : ~b.p0) & ((letter & 2u) ? b.p1 : ~b.p1);
+  return sel4(letter, b.c[0], b.c[1], b.c[2], b.c[3]) + (uint32_t)popc64(m & ((1ull << off) - 1ull));
+}
+
+// one backward-extension step of the half-open interval [lo,hi) by `letter` (0..4) with u32 pointers:
+// rank32 blocks for a,c,g,t (one sector when both bounds share a block), the unmodified .awfmi block
+// for x or when a poisoned block is met.  C32 = prefix sums as u32[6].
+NM_HD void lf_fast(const DevIndex &ix, const uint32_t *C32, unsigned letter, uint32_t &lo, uint32_t &hi) {
+  if (letter < 4u) {
+    const uint32_t blo = lo >> 6, bhi = hi >> 6;
+    const Rank32Block a = ld_rank32(ix.rank32, blo);
+    uint32_t nlo = occ_in_block(a, letter, lo & 63u), nhi;
+    bool poison = a.c[0] == kPoison;
+    if (bhi == blo) {
+      nhi = occ_in_block(a, letter, hi & 63u);
+    } else {
+      const Rank32Block b = ld_rank32(ix.rank32, bhi);
+      nhi = occ_in_block(b, letter, hi & 63u);
+      poison = poison || b.c[0] == kPoison;
+    }
+    if (!poison) {
+      const uint32_t c = C32[letter];
+      lo = c + nlo;
+      hi = c + nhi;
+      return;
+    }
+  }
+  const uint32_t c = C32[letter];
+  const uint32_t nlo = (uint32_t)occ_native(ix.native, letter, lo);
+  const uint32_t nhi = (uint32_t)occ_native(ix.native, letter, hi);
+  lo = c + nlo;
+  hi = c + nhi;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -286,6 +339,8 @@ struct SegParams {
   int out_width;  // 1, 2, 4
   int fast;       // rank32 + seed table usable for this search (kmin >= seed_len, bwt_len < 2^32-1)
   int want_ref_lf;
+  uint32_t dcap;   // first-pass depth cap of the trajectory-free search (characters, > seed_len)
+  uint32_t gsize;  // positions per certificate group of the deep pass
 };
 
 NM_HD void store_out(const SegParams &P, uint32_t i, uint32_t v) {
@@ -424,113 +479,190 @@ NM_HD uint32_t rc_seed_key(uint32_t fwdkey, uint32_t sl) {
 }
 
 // ---------------------------------------------------------------------------------------------
-// (F) trajectory-free search, fast kernel: one thread per position p runs two chains, interleaved:
-//   forward strand, leftwards from end e = p:   G[p] = min{ l : occ(seg[p-l, p)) == 1 }
-//   other strand,  rightwards from start i = p: R[p] = min{ l : occ(rc(seg[p, p+l))) == 0 }
-// both seeded from the seed table at depth seed_len (so values <= seed_len read as seed_len; the
-// caller guarantees kmin >= seed_len) and extended on the rank32 layout.  Anything irregular is
-// marked kPending for the generic kernel.  Why this gives the reference's bytes: DESIGN.md §3.
+// (F) trajectory-free search on the rank32 layout.  Two quantities per position p:
+//   forward strand, leftwards from end e = p:   G[p] = min{ l : occ(seg[p-l, p)) == 1 }   (kNone if none)
+//   other strand,  rightwards from start i = p: R[p] = min{ l : occ(rc(seg[p, p+l))) == 0 } (kInf if none)
+// each found by ONE backward search ("chain") seeded from the seed table at depth seed_len (values
+// below seed_len then read as seed_len; the caller guarantees kmin >= seed_len) or, when the seed
+// window holds a barrier / irregular letter / the segment edge, from depth 1.
+// Three passes keep long repeats cheap:
+//   pass 1 (free_fast_thread)   every position, chains capped at depth P.dcap -> value or kDeep
+//   pass 2 (free_cert_thread)   one thread per group of P.gsize positions: ONE chain from the group's
+//                               outermost kDeep position, run P.gsize deeper than kmax.  A string that
+//                               CONTAINS seg[e'-L, e') (resp. seg[i', i'+L)) and still occurs twice
+//                               (resp. still occurs on the other strand) proves the same of the
+//                               contained string, so one chain settles every kDeep position of a
+//                               group that lies in a long exact repeat
+//   pass 3 (free_rest_thread)   positions still kDeep: their own chain, uncapped
+// Why the resolved bytes equal the reference's: DESIGN.md section 3.
 // ---------------------------------------------------------------------------------------------
-struct Chain32 {
-  uint32_t lo, hi;  // half-open
-  uint32_t d;       // characters consumed
-  bool active;
+struct ChainResult {
+  uint32_t d_hit;   // depth at which the chain's stop condition was met (count == 1 / count == 0), 0 = never
+  uint32_t d_stop;  // depth explored; the count at every depth <= d_stop (and < d_hit) did not meet the condition
+  bool wall;        // stopped because the next character is a barrier or beyond the segment
 };
 
-NM_HD void free_fast_thread(const DevIndex &ix, const SegParams &P, uint32_t p, uint32_t &steps) {
+// forward strand: extend leftwards from end e (pattern seg[e-d, e)), stop when count == 1
+NM_HD ChainResult run_fwd_chain(const DevIndex &ix, const uint32_t *C32, const SegParams &P, uint32_t e,
+                                uint32_t maxdepth, uint32_t &steps) {
   const uint32_t sl = ix.seed_len;
-  uint32_t g = kNone, rr = kInf;
-  Chain32 f{0, 0, sl, false}, r{0, 0, sl, false};
-  bool poison = false;
+  ChainResult r{0, 0, false};
+  uint32_t lo, hi, d;
+  uint32_t key = kSeedInvalid;
+  if (e >= sl && !(P.mode == 1 && e == P.seg_len)) key = P.seedkey[e - sl];
+  if (key != kSeedInvalid) {
+    const SeedEntry32 s = ix.seed32[key];
+    lo = s.start;
+    hi = s.start + s.len;
+    d = sl;
+  } else {  // from depth 1 (the caller has checked that seg[e-1] is not a barrier)
+    const unsigned l = P.codes[e - 1] & kLetterMask;
+    lo = C32[l];
+    hi = C32[l + 1];
+    d = 1;
+  }
+  for (;;) {
+    const uint32_t n = hi - lo;
+    if (n <= 1u) {
+      if (n == 1u) r.d_hit = d;
+      else atomic_or64(&P.counters[CTR_ANOMALY], 1ull);  // a substring of the segment is absent from the index
+      r.d_stop = d;
+      return r;
+    }
+    if (d >= e) { r.wall = true; break; }
+    const uint8_t c = P.codes[e - 1 - d];
+    if (c & kBarrier) { r.wall = true; break; }
+    if (d >= maxdepth) break;
+    lf_fast(ix, C32, c & kLetterMask, lo, hi);
+    ++d;
+    ++steps;
+  }
+  r.d_stop = d;
+  return r;
+}
 
-  // ---- forward strand, end e = p
-  if (p >= 1 && !(P.codes[p - 1] & kBarrier)) {
-    uint32_t key = kSeedInvalid;
-    if (p >= sl && !(P.mode == 1 && p == P.seg_len)) key = P.seedkey[p - sl];
-    if (key == kSeedInvalid) {
-      g = kPending;
-    } else {
-      const SeedEntry32 s = ix.seed32[key];
-      f.lo = s.start;
-      f.hi = s.start + s.len;
-      if (s.len == 0) atomic_or64(&P.counters[CTR_ANOMALY], 1ull);
-      else if (s.len == 1) g = sl;
-      else f.active = true;
-    }
-  }
-  // ---- other strand, start i = p
-  const bool want_r = P.use_rc && p < P.num_kmers && !(P.codes[p] & kNoStart);
-  if (want_r) {
-    const uint32_t key = P.seedkey[p];
-    if (key == kSeedInvalid) {  // includes p + seed_len > seg_len, i.e. every truncated list-mode length < seed_len
-      rr = kPending;
-    } else {
-      const SeedEntry32 s = ix.seed32[rc_seed_key(key, sl)];
-      r.lo = s.start;
-      r.hi = s.start + s.len;
-      if (s.len == 0) rr = sl;
-      else r.active = true;
-    }
-  }
+NM_HD unsigned rc_letter_of_code(uint8_t c) {
+  const unsigned l = c & kLetterMask;
+  if (c & kIrregular) return l == 3u ? 3u : 4u;  // U/u keeps letter t (search.py:22 does not complement it)
+  return 3u - l;
+}
 
-  while (f.active || r.active) {
-    unsigned fl = 0, rl = 0;
-    if (f.active) {  // next character to the left: seg[p-1-d]
-      if (f.d >= P.kmax || f.d >= p) { f.active = false; g = kNone; }
-      else {
-        const uint8_t c = P.codes[p - 1 - f.d];
-        if (c & kBarrier) { f.active = false; g = kNone; }
-        else if (c & kIrregular) { f.active = false; g = kPending; }
-        else fl = c & 3u;
+// other strand: extend rightwards from start i (pattern rc(seg[i, i+d))), stop when count == 0
+NM_HD ChainResult run_rc_chain(const DevIndex &ix, const uint32_t *C32, const SegParams &P, uint32_t i,
+                               uint32_t maxdepth, uint32_t &steps) {
+  const uint32_t sl = ix.seed_len;
+  ChainResult r{0, 0, false};
+  uint32_t lo, hi, d;
+  const uint32_t key = P.seedkey[i];
+  if (key != kSeedInvalid) {
+    const SeedEntry32 s = ix.seed32[rc_seed_key(key, sl)];
+    lo = s.start;
+    hi = s.start + s.len;
+    d = sl;
+  } else {  // from depth 1 (the caller has checked that seg[i] may start a k-mer)
+    const unsigned l = rc_letter_of_code(P.codes[i]);
+    lo = C32[l];
+    hi = C32[l + 1];
+    d = 1;
+  }
+  for (;;) {
+    if (hi == lo) {
+      r.d_hit = d;
+      r.d_stop = d;
+      return r;
+    }
+    if (i + d >= P.seg_len) { r.wall = true; break; }
+    const uint8_t c = P.codes[i + d];
+    if (c & kBarrier) { r.wall = true; break; }
+    if (d >= maxdepth) break;
+    lf_fast(ix, C32, rc_letter_of_code(c), lo, hi);
+    ++d;
+    ++steps;
+  }
+  r.d_stop = d;
+  return r;
+}
+
+NM_HD bool fwd_wanted(const SegParams &P, uint32_t e) { return e >= 1 && !(P.codes[e - 1] & kBarrier); }
+NM_HD bool rc_wanted(const SegParams &P, uint32_t i) {
+  return P.use_rc && i < P.num_kmers && !(P.codes[i] & kNoStart);
+}
+
+// pass 1 and pass 3 share this: `cap` = P.dcap in pass 1, kmax in pass 3 (which only redoes kDeep entries)
+NM_HD void free_chain_thread(const DevIndex &ix, const uint32_t *C32, const SegParams &P, uint32_t p, bool first,
+                             uint32_t &steps) {
+  const uint32_t cap = first ? (P.dcap < P.kmax ? P.dcap : P.kmax) : P.kmax;
+  if (first || P.G[p] == kDeep) {
+    uint32_t g = kNone;
+    if (fwd_wanted(P, p)) {
+      const ChainResult r = run_fwd_chain(ix, C32, P, p, cap, steps);
+      if (r.d_hit) g = r.d_hit;
+      else if (!r.wall && r.d_stop < P.kmax && r.d_stop >= cap) g = kDeep;
+    }
+    P.G[p] = g;
+  }
+  if (p < P.seg_len && (first || P.R[p] == kDeep)) {
+    uint32_t rr = kInf;
+    if (rc_wanted(P, p)) {
+      const ChainResult r = run_rc_chain(ix, C32, P, p, cap, steps);
+      if (r.d_hit) rr = r.d_hit;
+      else if (!r.wall && r.d_stop < P.kmax && r.d_stop >= cap) rr = kDeep;
+    }
+    P.R[p] = rr;
+  }
+}
+
+// pass 2: group t covers ends e in (t*gs, (t+1)*gs] and starts i in [t*gs, (t+1)*gs)
+NM_HD void free_cert_thread(const DevIndex &ix, const uint32_t *C32, const SegParams &P, uint32_t t, uint32_t &steps) {
+  const uint32_t gs = P.gsize;
+  // ---- forward strand: chain from the LARGEST deep end e0; it contains seg[e'-L, e') for every smaller e'
+  {
+    const uint32_t first = t * gs + 1;
+    uint32_t last = first + gs - 1;
+    if (last > P.seg_len) last = P.seg_len;
+    uint32_t e0 = 0, emin = 0;
+    for (uint32_t e = first; e <= last; ++e)
+      if (P.G[e] == kDeep) { e0 = e; if (!emin) emin = e; }
+    if (e0) {
+      const ChainResult r = run_fwd_chain(ix, C32, P, e0, P.kmax + (e0 - emin), steps);
+      for (uint32_t e = emin; e <= e0; ++e) {
+        if (P.G[e] != kDeep) continue;
+        const uint32_t dt = e0 - e;
+        if (r.wall && r.d_stop <= dt) continue;          // e lies beyond the wall e0's chain ran into
+        uint32_t L = P.kmax;                             // deepest length e itself may be asked about
+        if (r.wall && r.d_stop - dt < L) L = r.d_stop - dt;
+        if (dt == 0) {
+          P.G[e] = (r.d_hit && r.d_hit <= L) ? r.d_hit : kNone;
+        } else if (L + dt <= r.d_stop && (r.d_hit == 0 || r.d_hit > L + dt)) {
+          P.G[e] = kNone;                                // seg[e-L, e0) occurs twice, so does seg[e-L, e)
+        }
       }
-    }
-    if (r.active) {  // next character to the right: seg[p+d], complemented
-      if (r.d >= P.kmax || p + r.d >= P.seg_len) { r.active = false; rr = kInf; }
-      else {
-        const uint8_t c = P.codes[p + r.d];
-        if (c & kBarrier) { r.active = false; rr = kInf; }
-        else if (c & kIrregular) { r.active = false; rr = kPending; }
-        else rl = 3u - (c & 3u);
-      }
-    }
-    uint32_t flo = 0, fhi = 0, rlo = 0, rhi = 0;
-    if (f.active) {
-      flo = occ_rank32(ix.rank32, fl, f.lo, poison);
-      fhi = occ_rank32(ix.rank32, fl, f.hi, poison);
-    }
-    if (r.active) {
-      rlo = occ_rank32(ix.rank32, rl, r.lo, poison);
-      rhi = occ_rank32(ix.rank32, rl, r.hi, poison);
-    }
-    if (poison) {  // a block with an x/$ symbol was touched: both searches go to the generic kernel
-      if (f.active) g = kPending;
-      if (r.active) rr = kPending;
-      break;
-    }
-    if (f.active) {
-      const uint32_t c = (uint32_t)ix.C[fl];
-      f.lo = c + flo;
-      f.hi = c + fhi;
-      ++f.d;
-      ++steps;
-      const uint32_t n = f.hi - f.lo;
-      if (n <= 1) {
-        f.active = false;
-        if (n == 1) g = f.d;
-        else atomic_or64(&P.counters[CTR_ANOMALY], 1ull);  // a substring of the segment is absent from the index
-      }
-    }
-    if (r.active) {
-      const uint32_t c = (uint32_t)ix.C[rl];
-      r.lo = c + rlo;
-      r.hi = c + rhi;
-      ++r.d;
-      ++steps;
-      if (r.hi == r.lo) { r.active = false; rr = r.d; }
     }
   }
-  P.G[p] = g;
-  if (p < P.seg_len) P.R[p] = (p < P.num_kmers) ? rr : kInf;
+  // ---- other strand: chain from the SMALLEST deep start i0; it contains seg[i', i'+L) for every larger i'
+  if (P.use_rc) {
+    const uint32_t first = t * gs;
+    uint32_t end = first + gs;
+    if (end > P.num_kmers) end = P.num_kmers;
+    uint32_t i0 = kNoBarrier, imax = 0;
+    for (uint32_t i = first; i < end; ++i)
+      if (P.R[i] == kDeep) { if (i0 == kNoBarrier) i0 = i; imax = i; }
+    if (i0 != kNoBarrier) {
+      const ChainResult r = run_rc_chain(ix, C32, P, i0, P.kmax + (imax - i0), steps);
+      for (uint32_t i = i0; i <= imax; ++i) {
+        if (P.R[i] != kDeep) continue;
+        const uint32_t dt = i - i0;
+        if (r.wall && r.d_stop <= dt) continue;
+        uint32_t L = P.kmax;
+        if (r.wall && r.d_stop - dt < L) L = r.d_stop - dt;
+        if (dt == 0) {
+          P.R[i] = (r.d_hit && r.d_hit <= L) ? r.d_hit : kInf;
+        } else if (L + dt <= r.d_stop && (r.d_hit == 0 || r.d_hit > L + dt)) {
+          P.R[i] = kInf;                                 // rc(seg[i0, i+L)) still occurs, so does rc(seg[i, i+L))
+        }
+      }
+    }
+  }
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -539,12 +671,6 @@ NM_HD void free_fast_thread(const DevIndex &ix, const SegParams &P, uint32_t p, 
 // pointers.  Runs for entries marked kPending, or for every position when `all` is set
 // (kmin < seed_len, or bwt_len >= 2^32-1).
 // ---------------------------------------------------------------------------------------------
-NM_HD unsigned rc_letter_of_code(uint8_t c) {
-  const unsigned l = c & kLetterMask;
-  if (c & kIrregular) return l == 3u ? 3u : 4u;  // U/u keeps letter t (search.py:22 does not complement it)
-  return 3u - l;
-}
-
 NM_HD void free_generic_thread(const DevIndex &ix, const SegParams &P, uint32_t p, bool all, uint32_t &steps,
                                uint32_t &nsearch) {
   // ---- forward strand, end e = p

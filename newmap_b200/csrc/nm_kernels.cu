@@ -63,10 +63,30 @@ __global__ void __launch_bounds__(kBlock) k_trajectory(DevIndex ix, SegParams P)
   flush_counter(&P.counters[CTR_QUERIES], nq);
 }
 
-__global__ void __launch_bounds__(kBlock) k_free_fast(DevIndex ix, SegParams P) {
+// prefix sums as u32[6] staged in shared memory (dynamic indexing of kernel parameters would spill to local memory)
+__device__ __forceinline__ const uint32_t *stage_c32(const DevIndex &ix, uint32_t *sC) {
+  if (threadIdx.x < 6) sC[threadIdx.x] = ix.c32[threadIdx.x];
+  __syncthreads();
+  return sC;
+}
+
+// pass 1 (first = true): every position, depth-capped; pass 3 (first = false): positions still kDeep
+__global__ void __launch_bounds__(kBlock, 8) k_free_chain(DevIndex ix, SegParams P, bool first) {
+  __shared__ uint32_t sC[8];
+  const uint32_t *C32 = stage_c32(ix, sC);
   const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
   uint32_t steps = 0;
-  if (p <= P.seg_len) free_fast_thread(ix, P, p, steps);
+  if (p <= P.seg_len) free_chain_thread(ix, C32, P, p, first, steps);
+  flush_counter(&P.counters[CTR_LF], steps);
+}
+
+// pass 2: one thread per group of P.gsize positions
+__global__ void __launch_bounds__(kBlock, 8) k_free_cert(DevIndex ix, SegParams P, uint32_t ngroups) {
+  __shared__ uint32_t sC[8];
+  const uint32_t *C32 = stage_c32(ix, sC);
+  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  uint32_t steps = 0;
+  if (t < ngroups) free_cert_thread(ix, C32, P, t, steps);
   flush_counter(&P.counters[CTR_LF], steps);
 }
 
@@ -157,7 +177,13 @@ void launch_trajectory(const DevIndex &ix, const SegParams &P, cudaStream_t st) 
   k_trajectory<<<grid_for(P.num_kmers), kBlock, 0, st>>>(ix, P);
 }
 void launch_free_fast(const DevIndex &ix, const SegParams &P, cudaStream_t st) {
-  k_free_fast<<<grid_for((uint64_t)P.seg_len + 1), kBlock, 0, st>>>(ix, P);
+  const uint64_t n = (uint64_t)P.seg_len + 1;
+  k_free_chain<<<grid_for(n), kBlock, 0, st>>>(ix, P, true);
+  if (P.dcap < P.kmax) {
+    const uint32_t ngroups = (uint32_t)((n + P.gsize - 1) / P.gsize);
+    k_free_cert<<<grid_for(ngroups, 64), 64, 0, st>>>(ix, P, ngroups);
+    k_free_chain<<<grid_for(n), kBlock, 0, st>>>(ix, P, false);
+  }
 }
 void launch_free_generic(const DevIndex &ix, const SegParams &P, bool all, cudaStream_t st) {
   k_free_generic<<<grid_for((uint64_t)P.seg_len + 1), kBlock, 0, st>>>(ix, P, all);

@@ -38,7 +38,7 @@ struct nm_index {
   uint32_t sa_ratio = 0;
   bool has_rank32 = false;
   uint64_t device_bytes = 0;
-  void *d_native = nullptr, *d_rank32 = nullptr, *d_seed32 = nullptr, *d_seed64 = nullptr;
+  void *d_native = nullptr, *d_rank32 = nullptr, *d_seed32 = nullptr, *d_seed64 = nullptr, *d_c32 = nullptr;
   nm_workspace *default_ws = nullptr;  // used by nm_min_unique
   std::mutex mu;                       // serialises calls that share default_ws / count scratch
 };
@@ -167,6 +167,11 @@ int load_index(const char *path, int device, nm_index **out) {
     nm::launch_seed_transcode(ix->dev.seed64, (nm::SeedEntry32 *)ix->d_seed32, ix->seed_entries, 0);
     NM_CUDA(cudaGetLastError());
     NM_CUDA(cudaDeviceSynchronize());
+    uint32_t c32[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (int l = 0; l < 6; ++l) c32[l] = (uint32_t)prefix[l];
+    if (cudaMalloc(&ix->d_c32, sizeof c32) != cudaSuccess) return NM_EALLOC;
+    NM_CUDA(cudaMemcpy(ix->d_c32, c32, sizeof c32, cudaMemcpyHostToDevice));
+    ix->dev.c32 = (const uint32_t *)ix->d_c32;
     ix->dev.rank32 = (const uint32_t *)ix->d_rank32;
     ix->dev.seed32 = (const nm::SeedEntry32 *)ix->d_seed32;
     ix->has_rank32 = true;
@@ -215,7 +220,7 @@ int run_search(nm_workspace *ws, int algo) {
     P.fast = fast ? 1 : 0;
     if (fast) nm::launch_free_fast(ix->dev, P, st);
     NM_CUDA(cudaEventRecord(ws->ev[EV_SEARCH1], st));
-    nm::launch_free_generic(ix->dev, P, !fast, st);
+    if (!fast) nm::launch_free_generic(ix->dev, P, true, st);
     NM_CUDA(cudaEventRecord(ws->ev[EV_GENERIC1], st));
     nm::launch_resolve(ix->dev, P, st);
     NM_CUDA(cudaEventRecord(ws->ev[EV_RESOLVE1], st));
@@ -270,6 +275,7 @@ void nm_index_close(nm_index *ix) {
   cudaFree(ix->d_rank32);
   cudaFree(ix->d_seed32);
   cudaFree(ix->d_seed64);
+  cudaFree(ix->d_c32);
   delete ix;
 }
 
@@ -448,6 +454,14 @@ int nm_workspace_search(nm_workspace *ws, uint64_t num_kmers, int mode, const ui
   P.out_width = out_width;
   P.fast = 0;
   P.want_ref_lf = 1;
+  {  // first-pass depth cap: seed + 12 characters unless overridden (tuning knob, results do not depend on it)
+    static const int env_dcap = getenv("NEWMAP_B200_DCAP") ? atoi(getenv("NEWMAP_B200_DCAP")) : 0;
+    static const int env_gs = getenv("NEWMAP_B200_GSIZE") ? atoi(getenv("NEWMAP_B200_GSIZE")) : 0;
+    const uint32_t sl = ws->ix->dev.seed_len;
+    P.dcap = env_dcap > 0 ? (uint32_t)env_dcap : sl + 12;
+    if (P.dcap <= sl) P.dcap = sl + 1;
+    P.gsize = env_gs > 0 ? (uint32_t)env_gs : 32;
+  }
   ws->algo_req = algo;
   ws->have_search = true;
   ws->timed_d2h = false;

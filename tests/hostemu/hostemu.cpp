@@ -17,6 +17,7 @@ struct EmuIndex {
   std::vector<uint32_t> rank32;
   std::vector<SeedEntry32> seed32;
   std::vector<uint64_t> seed64;
+  uint32_t c32[8] = {0};
   DevIndex dev{};
   bool has_rank32 = false;
 };
@@ -54,6 +55,8 @@ EmuIndex *emu_index_open(const char *path) {
   for (uint64_t t = 0; t < n64; ++t) transcode_thread(ix->native.data(), nb, bwt_len, ix->rank32.data(), t);
   ix->seed32.resize(entries);
   for (uint64_t t = 0; t < entries; ++t) seed_transcode_thread(ix->seed64.data(), ix->seed32.data(), t);
+  for (int l = 0; l < 6; ++l) ix->c32[l] = (uint32_t)prefix[l];
+  ix->dev.c32 = ix->c32;
   ix->dev.rank32 = ix->rank32.data();
   ix->dev.seed32 = ix->seed32.data();
   ix->has_rank32 = true;
@@ -76,7 +79,7 @@ int emu_count(EmuIndex *ix, const uint8_t *seq, uint64_t seq_len, const uint64_t
 // stats: [0] lf, [1] queries, [2] generic searches, [3] anomaly, [4] zero pos (-1), [5] zero len, [6] zero round, [7] ref lf
 int emu_min_unique(EmuIndex *ix, const uint8_t *seg, uint32_t seg_len, uint32_t num_kmers, int mode,
                    const uint32_t *klist, uint32_t nk, uint32_t initial, int use_rc, int algo, int out_width,
-                   void *out, int64_t *stats) {
+                   void *out, int64_t *stats, uint32_t dcap, uint32_t gsize) {
   std::vector<uint8_t> codes(seg_len + 16);
   std::vector<uint32_t> seedkey(seg_len + 1), nb(seg_len + 1), tf((seg_len + kTile - 1) / kTile + 1), G(seg_len + 2), R(seg_len + 1);
   unsigned long long ctr[CTR_N] = {0, 0, 0, 0, ~0ull, 0, 0, 0};
@@ -85,6 +88,8 @@ int emu_min_unique(EmuIndex *ix, const uint8_t *seg, uint32_t seg_len, uint32_t 
   P.G = G.data(); P.R = R.data(); P.out = out; P.klist = klist; P.counters = ctr;
   P.seg_len = seg_len; P.num_kmers = num_kmers; P.nk = nk; P.initial = initial; P.mode = mode;
   P.use_rc = use_rc; P.out_width = out_width; P.want_ref_lf = 1;
+  P.dcap = dcap ? dcap : ix->dev.seed_len + 12; if (P.dcap <= ix->dev.seed_len) P.dcap = ix->dev.seed_len + 1;
+  P.gsize = gsize ? gsize : 32;
   if (mode == 0) { P.kmin = klist[0]; P.kmax = klist[1]; }
   else { P.kmin = P.kmax = klist[0]; for (uint32_t j = 0; j < nk; ++j) { if (klist[j] < P.kmin) P.kmin = klist[j]; if (klist[j] > P.kmax) P.kmax = klist[j]; } }
   for (uint32_t p = 0; p < seg_len; ++p) prep_thread(ix->dev, P, p);
@@ -97,8 +102,19 @@ int emu_min_unique(EmuIndex *ix, const uint8_t *seg, uint32_t seg_len, uint32_t 
   } else {
     const bool fast = (algo != 2) && ix->has_rank32 && P.kmin >= ix->dev.seed_len;
     P.fast = fast;
-    if (fast) for (uint32_t p = 0; p <= seg_len; ++p) free_fast_thread(ix->dev, P, p, steps);
-    for (uint32_t p = 0; p <= seg_len; ++p) free_generic_thread(ix->dev, P, p, !fast, steps, ns);
+    if (fast) {
+      for (uint32_t p = 0; p <= seg_len; ++p) free_chain_thread(ix->dev, ix->c32, P, p, true, steps);
+      if (P.dcap < P.kmax) {
+        const uint32_t ngroups = (seg_len + 1 + P.gsize - 1) / P.gsize;
+        uint32_t s2 = 0;
+        for (uint32_t t = 0; t < ngroups; ++t) free_cert_thread(ix->dev, ix->c32, P, t, s2);
+        ns = s2;  // reported in stats[2]: LF steps of the certificate pass
+        steps += s2;
+        for (uint32_t p = 0; p <= seg_len; ++p) free_chain_thread(ix->dev, ix->c32, P, p, false, steps);
+      }
+    } else {
+      for (uint32_t p = 0; p <= seg_len; ++p) free_generic_thread(ix->dev, P, p, true, steps, ns);
+    }
     for (uint32_t i = 0; i < num_kmers; ++i) resolve_thread(ix->dev, P, i, ref_lf);
   }
   if (stats) {

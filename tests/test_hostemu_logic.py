@@ -117,3 +117,25 @@ def test_random_small_genomes_all_algorithms_agree_with_oracle(tmp_path):
                 for algo in (0, 1, 2):
                     got, st = e.min_unique_segment(seg.data, n, klist, is_range, algo=algo)
                     assert np.array_equal(got, want), (trial, klist[:3], is_range, algo, batch)
+
+
+@pytest.mark.parametrize("dcap_extra,gsize", [(1, 1), (1, 5), (2, 32), (4, 64), (12, 32), (3, 200), (1000, 32)])
+def test_certificate_pass_is_exact_for_any_cap_and_group(manifest, golden_searches, dcap_extra, gsize):
+    """The depth cap and the certificate group size are tuning knobs: results never depend on them."""
+    cache = {}
+    for run in manifest["searches"]:
+        if run["index"].startswith("genome"):
+            continue
+        ix = cache.setdefault(run["index"], EmuIndex(GOLD / f"{run['index']}.awfmi"))
+        seed = manifest["indexes"][run["index"]]["seed_length"]
+        klist = run_klist(run)
+        got = {}
+        for seg, n in _segments(run):
+            out, stats = ix.min_unique_segment(seg.data, n, klist, run["range"], run.get("initial", 0),
+                                               not run.get("norc", False), 0, dcap=seed + dcap_extra, gsize=gsize)
+            got.setdefault(seg.id, []).append(out)
+        for sid, parts in got.items():
+            want = golden_searches[f"run{run['id']}|{sid.decode()}"]
+            arr = np.concatenate(parts)
+            bad = np.nonzero(arr != want)[0]
+            assert bad.size == 0, (dcap_extra, gsize, run, sid, bad[:10], arr[bad[:10]], want[bad[:10]])

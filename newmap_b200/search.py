@@ -61,6 +61,8 @@ class SearchConfig:
     verbose: bool = False
     device: int | None = None            # CUDA device (default: $NEWMAP_B200_DEVICE, $LOCAL_RANK, 0)
     algorithm: str = "auto"              # "auto" | "trajectory" | "free_generic" (include/newmap_b200.h)
+    rank: int = 0                        # position sharding: this process handles the segments whose running
+    world_size: int = 1                  # number (over the whole FASTA) is congruent to rank modulo world_size
     log: Callable[..., None] = field(init=False, repr=False, compare=False)
 
     def __post_init__(self):
@@ -104,7 +106,8 @@ class SearchConfig:
                    include_sequence_ids=include, exclude_sequence_ids=exclude, verbose=args.verbose,
                    num_threads=args.num_threads, kmer_batch_size=args.kmer_batch_size,
                    initial_search_length=args.initial_search_length,
-                   device=getattr(args, "device", None), algorithm=getattr(args, "algorithm", "auto"))
+                   device=getattr(args, "device", None), algorithm=getattr(args, "algorithm", "auto"),
+                   rank=int(os.environ.get("RANK", "0")), world_size=int(os.environ.get("WORLD_SIZE", "1")))
 
 
 # ------------------------------------------------------------------------------------------------
@@ -243,9 +246,14 @@ def write_unique_counts(config: SearchConfig):
     sequence_processed = False
     current_sequence_id = b""
     current_file = None
+    sharded = config.world_size > 1
+    if not 0 <= config.rank < config.world_size:
+        raise ValueError("rank must be in [0, world_size)")
+    segment_number = -1          # running number over all processed segments: the sharding key
+    segment_in_sequence = 0      # window number inside the current sequence: the file offset key
 
     def finish(slot: _Slot):
-        seg, num_kmers, fh = slot.job
+        seg, num_kmers, fh, offset = slot.job
         st = slot.ws.sync()
         if st.zero_pos >= 0:
             _raise_zero_count(seg.data, st)
@@ -261,7 +269,11 @@ def write_unique_counts(config: SearchConfig):
                 totals["min_len"] = min(totals["min_len"], int(res[res != 0].min()))
             else:
                 config.log("No unique lengths found for this sequence segment")
-        res.tofile(fh)
+        # every segment lands at window_number * batch of <id>.unique.uintN (host-side gather: ranks share
+        # the files, nothing is exchanged between GPUs); with one rank this is the reference's append
+        os.pwrite(fh.fileno(), res.tobytes(), offset * data_type.itemsize)
+        if seg.epilogue:
+            os.ftruncate(fh.fileno(), (offset + num_kmers) * data_type.itemsize)
         slot.job = None
 
     def drain():
@@ -287,9 +299,21 @@ def write_unique_counts(config: SearchConfig):
                     segment.id.decode(), unique_count_suffix)
                 if current_file is not None:
                     current_file.close()
-                current_file = stack.enter_context(open(path, "wb"))   # truncates, then appended per segment
+                # one rank: truncate like search.py:305.  Several ranks share the file: create without truncating
+                # (another rank may already have written its windows); the rank that owns the epilogue sets the size.
+                if sharded:
+                    fd = os.open(path, os.O_RDWR | os.O_CREAT, 0o644)
+                    current_file = stack.enter_context(os.fdopen(fd, "r+b"))
+                else:
+                    current_file = stack.enter_context(open(path, "wb"))
+                segment_in_sequence = 0
                 config.log("Writing unique lengths for sequence ID: {}".format(segment.id.decode()))
             num_kmers = get_num_kmers(segment, max_kmer_length)
+            segment_number += 1
+            offset = segment_in_sequence * config.kmer_batch_size
+            segment_in_sequence += 1
+            if segment_number % config.world_size != config.rank:
+                continue
             config.log("Processing {} k-mers".format(num_kmers))
             if len(inflight) >= PIPELINE_DEPTH:
                 finish(inflight.popleft())
@@ -299,7 +323,7 @@ def write_unique_counts(config: SearchConfig):
                 slots.append(slot)
             n = len(segment.data)
             slot.inp.array[:n] = np.frombuffer(segment.data, dtype=np.uint8)
-            slot.job = (segment, num_kmers, current_file)
+            slot.job = (segment, num_kmers, current_file, offset)
             slot.ws.upload(slot.inp.ptr, n)
             slot.ws.search(num_kmers, config.kmer_lengths, config.is_binary_search, config.initial_search_length,
                            config.use_reverse_complement, config.algorithm, data_type.itemsize)

@@ -124,6 +124,17 @@ int nm_workspace_checksum(nm_workspace *ws, uint64_t *sum);
 void *nm_host_alloc(uint64_t bytes);
 void nm_host_free(void *p);
 
+/* GPU construction of a reference-format .awfmi (v8, DNA), byte-identical to what the reference's
+ * CPU builder writes (AwFmCreate.c:128-389 awFmCreateIndexFromFasta + AwFmFile.c:20-171), from the
+ * three FastaVector buffers of the FASTA (lib/FastaVector/src/FastaVector.c:50-168): `sequence` = all
+ * sequences concatenated with a '\0' after each, `header` = header lines each followed by '\0',
+ * `metadata` = metadata_count pairs {headerEndPosition, sequenceEndPosition}.  bwtLength must stay
+ * below 2^32-16.  seconds_sort (optional) receives the device time of the suffix sort. */
+int nm_index_build(const uint8_t *sequence, uint64_t sequence_len, const uint8_t *header, uint64_t header_len,
+                   const uint64_t *metadata, uint64_t metadata_count, uint32_t sa_ratio, uint32_t seed_len,
+                   int device, const char *out_path, double *seconds_sort);
+const char *nm_build_last_error(void);
+
 /* Random-access roofline probe: `chains` threads each walk `mlp` (1, 2 or 4) independent chains of
  * `steps` dependent loads of `granule` bytes (32, 64 or 128, granule-aligned) at pseudo-random
  * offsets of a `bytes`-sized (power of two) device buffer.  Returns loads/second (CUDA events). */

@@ -57,6 +57,8 @@ SIGNATURES = {
     "nm_workspace_checksum": (_i, [_vp, C.POINTER(_u64)]),
     "nm_host_alloc": (_vp, [_u64]),
     "nm_host_free": (None, [_vp]),
+    "nm_index_build": (_i, [_vp, _u64, _vp, _u64, _vp, _u64, _u32, _u32, _i, C.c_char_p, C.POINTER(C.c_double)]),
+    "nm_build_last_error": (C.c_char_p, []),
     "nm_probe_random_access": (_i, [_i, _u64, _u32, _u64, _u32, _u32, C.POINTER(C.c_double), C.POINTER(C.c_float)]),
 }
 

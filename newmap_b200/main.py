@@ -5,7 +5,7 @@ from __future__ import annotations
 import sys
 from argparse import ArgumentParser
 
-from . import __version__, search
+from . import __version__, index, search
 from .util import INDEX_EXTENSION
 
 DEFAULT_KMER_BATCH_SIZE = 10000000
@@ -19,6 +19,13 @@ def build_parser() -> ArgumentParser:
                                                        "position of a reference sequence")
     parser.add_argument("--version", action="version", version=f"%(prog)s-b200 {__version__}")
     sub = parser.add_subparsers(metavar="", required=True)
+    b = sub.add_parser("index", help="Create an FM index from sequences (on the GPU, reference file format)")
+    b.set_defaults(func=index.main)
+    b.add_argument("fasta_file", help="Reference sequence file in FASTA format")
+    b.add_argument("--output", "-i", metavar="FILE", default=None,
+                   help=f"index file to write (default: basename of fasta_file with the {INDEX_EXTENSION} extension)")
+    b.add_argument("--compression-ratio", "-c", type=int, default=index.DEFAULT_COMPRESSION_RATIO)
+    b.add_argument("--seed-length", "-s", type=int, default=index.DEFAULT_SEED_LENGTH)
     p = sub.add_parser("search", help="Find the shortest unique sequence length at each position in sequences")
     p.set_defaults(func=search.main)
     p.add_argument("fasta_file", metavar=FASTA_FILE_METAVAR, help="(gzipped) fasta file for kmer generation")

@@ -64,13 +64,31 @@ def prepare_workload(name: str) -> tuple[Path, Path]:
     t0 = time.time()
     synth.write_fasta(fa, synth.make_genome(lengths, seed))
     log(f"[bench] genome {name}: {sum(lengths)} bp written in {time.time() - t0:.1f}s")
-    from oracle import ora   # the reference's index builder lives in oracle/_ref (not on the timed path)
-    if not ora.ref_available():
-        raise SystemExit("bench: oracle/_ref (reference index builder) is missing; run __graft_entry__.build() "
-                         "where /root/reference exists")
+    builder = os.environ.get("NEWMAP_B200_INDEX_BUILDER", "auto")
     t0 = time.time()
-    ora.ref_build_index(fa, ix, SA_RATIO, SEED_LEN)
-    log(f"[bench] reference index built in {time.time() - t0:.1f}s ({ix.stat().st_size / 1e6:.0f} MB)")
+    built = None
+    if builder in ("auto", "gpu"):
+        # index construction is setup, not the timed path: use the GPU builder (writes the reference builder's
+        # file byte for byte -- tests/test_gpu_build.py) when a CUDA device is there, else the reference's own
+        try:
+            from newmap_b200 import _lib, index
+            if _lib.load().nm_device_count() > 0:
+                secs = index.generate_fm_index(fa, ix, SA_RATIO, SEED_LEN,
+                                               device=int(os.environ.get("LOCAL_RANK", "0")))
+                built = f"GPU builder (suffix sort {secs:.1f}s on device)"
+        except Exception as e:     # fall through to the reference builder
+            if builder == "gpu":
+                raise
+            log(f"[bench] GPU index build failed ({e}); using the reference builder")
+    if built is None:
+        from oracle import ora   # the reference's index builder lives in oracle/_ref (not on the timed path)
+        if not ora.ref_available():
+            raise SystemExit("bench: oracle/_ref (reference index builder) is missing; run __graft_entry__.build() "
+                             "where /root/reference exists")
+        ora.ref_build_index(fa, ix, SA_RATIO, SEED_LEN)
+        built = "reference builder (oracle/_ref)"
+    log(f"[bench] index built by {built} in {time.time() - t0:.1f}s ({ix.stat().st_size / 1e6:.0f} MB)")
+    (d / "builder.txt").write_text(built)
     done.write_text("ok")
     return fa, ix
 
@@ -182,7 +200,7 @@ def main():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default=os.environ.get("NEWMAP_B200_WORKLOAD", "c2_100m"), choices=list(WORKLOADS))
+    ap.add_argument("--workload", default=os.environ.get("NEWMAP_B200_WORKLOAD", "c3_1g"), choices=list(WORKLOADS))
     ap.add_argument("--segments-per-step", type=int, default=10)
     ap.add_argument("--cpu-sample", type=int, default=int(os.environ.get("NEWMAP_B200_CPU_SAMPLE", "1000000")))
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -196,7 +214,7 @@ def main():
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
             "config": {"workload": WORKLOADS[args.workload], "workload_id": args.workload,
-                       "kmer_batch_size": BATCH, "index": f"reference-built .awfmi, seed {SEED_LEN}, SA ratio {SA_RATIO}",
+                       "kmer_batch_size": BATCH, "index": f".awfmi v8 (reference format), seed {SEED_LEN}, SA ratio {SA_RATIO}",
                        "parallelism": f"index replicated x{world}, segments sharded, no collective"}}
 
     # ---------------- reference arm: CPU only, rank 0 only
@@ -233,6 +251,8 @@ def main():
     fa, ix_path = prepare_workload(args.workload)
 
     from newmap_b200 import _lib
+    builder_note = (CACHE / args.workload / "builder.txt")
+    base["config"]["index"] += "; built by " + (builder_note.read_text() if builder_note.is_file() else "unknown")
     kl = list(range(K_RANGE[0], K_RANGE[1] + 1))
     S = args.segments_per_step
     (segs, total_segments) = load_segments(fa, rank * S, S)

@@ -135,11 +135,13 @@ int nm_index_build(const uint8_t *sequence, uint64_t sequence_len, const uint8_t
                    int device, const char *out_path, double *seconds_sort);
 const char *nm_build_last_error(void);
 
-/* Random-access roofline probe: `chains` threads each walk `mlp` (1, 2 or 4) independent chains of
- * `steps` dependent loads of `granule` bytes (32, 64 or 128, granule-aligned) at pseudo-random
- * offsets of a `bytes`-sized (power of two) device buffer.  Returns loads/second (CUDA events). */
+/* Random-access roofline probe: `chains` threads each issue, `steps` times, `mlp` (1, 2, 4 or 8) loads of
+ * `granule` bytes (32, 64 or 128, granule-aligned) at pseudo-random offsets of a `bytes`-sized (power of
+ * two) device buffer.  dependent != 0: the next offset of each of the mlp chains depends on the data
+ * loaded (like the LF steps of a search); dependent == 0: all loads are independent (the ceiling of the
+ * memory system for random granules).  Returns loads/second (CUDA events). */
 int nm_probe_random_access(int device, uint64_t bytes, uint32_t granule, uint64_t chains, uint32_t steps,
-                           uint32_t mlp, double *loads_per_second, float *ms);
+                           uint32_t mlp, int dependent, double *loads_per_second, float *ms);
 
 #ifdef __cplusplus
 }

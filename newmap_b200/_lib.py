@@ -59,7 +59,7 @@ SIGNATURES = {
     "nm_host_free": (None, [_vp]),
     "nm_index_build": (_i, [_vp, _u64, _vp, _u64, _vp, _u64, _u32, _u32, _i, C.c_char_p, C.POINTER(C.c_double)]),
     "nm_build_last_error": (C.c_char_p, []),
-    "nm_probe_random_access": (_i, [_i, _u64, _u32, _u64, _u32, _u32, C.POINTER(C.c_double), C.POINTER(C.c_float)]),
+    "nm_probe_random_access": (_i, [_i, _u64, _u32, _u64, _u32, _u32, _i, C.POINTER(C.c_double), C.POINTER(C.c_float)]),
 }
 
 _lib = None
@@ -293,8 +293,9 @@ def checksum_host(arr: np.ndarray) -> int:
         return int(h.sum(dtype=np.uint64))
 
 
-def probe_random_access(device: int, nbytes: int, granule: int, chains: int, steps: int, mlp: int = 1):
+def probe_random_access(device: int, nbytes: int, granule: int, chains: int, steps: int, mlp: int = 1,
+                        dependent: bool = True):
     rate, ms = C.c_double(0), C.c_float(0)
-    check(load().nm_probe_random_access(device, int(nbytes), granule, int(chains), steps, mlp, C.byref(rate), C.byref(ms)),
+    check(load().nm_probe_random_access(device, int(nbytes), granule, int(chains), steps, mlp, int(dependent), C.byref(rate), C.byref(ms)),
           "nm_probe_random_access")
     return rate.value, ms.value

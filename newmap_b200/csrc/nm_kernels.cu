@@ -114,26 +114,29 @@ __global__ void __launch_bounds__(kBlock) k_checksum(const void *out, int width,
   flush_counter64(sum, acc);
 }
 
-// random-access probe: every thread walks MLP independent chains; the next offset of a chain depends
-// on the data it loaded, so loads of one chain are serialised exactly like the LF steps of one search.
-// n_granules must be a power of two (mask instead of a 64-bit modulo keeps the probe memory-bound).
-template <int WORDS, int MLP>  // 32-bit words per granule: 8, 16, 32
-__global__ void __launch_bounds__(kBlock) k_probe(const uint32_t *buf, uint64_t granule_mask, uint64_t chains,
+// random-access probe.  DEP = true: every thread walks MLP chains whose next offset depends on the data just
+// loaded (loads of one chain are serialised exactly like the LF steps of one search).  DEP = false: the
+// offsets depend only on (thread, step), so all loads of a thread are independent -- the most the memory
+// system can do on random granules.  n_granules is a power of two; 32-bit hashing keeps the ALU work small.
+__device__ __forceinline__ uint32_t mix32(uint32_t x) {
+  x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16;
+  return x;
+}
+template <int WORDS, int MLP, bool DEP>
+__global__ void __launch_bounds__(kBlock) k_probe(const uint32_t *buf, uint32_t granule_mask, uint64_t chains,
                                                   uint32_t steps, unsigned long long *sink) {
   const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= chains) return;
-  uint64_t x[MLP];
+  uint32_t x[MLP];
 #pragma unroll
-  for (int m = 0; m < MLP; ++m) x[m] = (t * MLP + m) * 0x9E3779B97F4A7C15ull + 0x1234567ull;
+  for (int m = 0; m < MLP; ++m) x[m] = mix32((uint32_t)(t * MLP + m) * 0x9E3779B9u + 0x1234567u);
   uint32_t acc = 0;
   for (uint32_t s = 0; s < steps; ++s) {
     uint32_t v[MLP];
 #pragma unroll
     for (int m = 0; m < MLP; ++m) {
-      x[m] ^= x[m] >> 29;
-      x[m] *= 0xBF58476D1CE4E5B9ull;
-      x[m] ^= x[m] >> 32;
-      const uint4 *p = reinterpret_cast<const uint4 *>(buf + (x[m] & granule_mask) * WORDS);
+      x[m] = mix32(x[m] + s);
+      const uint4 *p = reinterpret_cast<const uint4 *>(buf + (size_t)(x[m] & granule_mask) * WORDS);
       uint32_t a = 0;
 #pragma unroll
       for (int j = 0; j < WORDS / 4; ++j) {
@@ -145,7 +148,7 @@ __global__ void __launch_bounds__(kBlock) k_probe(const uint32_t *buf, uint64_t 
 #pragma unroll
     for (int m = 0; m < MLP; ++m) {
       acc += v[m];
-      x[m] += v[m];  // data dependence
+      if (DEP) x[m] += v[m];  // data dependence
     }
   }
   if (acc == 0x7fffffffu) atomicAdd(sink, 1ull);
@@ -198,20 +201,27 @@ void launch_checksum(const void *out, int out_width, uint64_t n, unsigned long l
   if (g > 148 * 8) g = 148 * 8;
   k_checksum<<<g, kBlock, 0, st>>>(out, out_width, n, sum);
 }
-template <int WORDS>
-static void launch_probe_w(const uint32_t *b, uint64_t mask, uint64_t chains, uint32_t steps, uint32_t mlp,
+template <int WORDS, bool DEP>
+static void launch_probe_w(const uint32_t *b, uint32_t mask, uint64_t chains, uint32_t steps, uint32_t mlp,
                            unsigned long long *sink, cudaStream_t st) {
-  if (mlp >= 4) k_probe<WORDS, 4><<<grid_for(chains), kBlock, 0, st>>>(b, mask, chains, steps, sink);
-  else if (mlp >= 2) k_probe<WORDS, 2><<<grid_for(chains), kBlock, 0, st>>>(b, mask, chains, steps, sink);
-  else k_probe<WORDS, 1><<<grid_for(chains), kBlock, 0, st>>>(b, mask, chains, steps, sink);
+  if (mlp >= 8) k_probe<WORDS, 8, DEP><<<grid_for(chains), kBlock, 0, st>>>(b, mask, chains, steps, sink);
+  else if (mlp >= 4) k_probe<WORDS, 4, DEP><<<grid_for(chains), kBlock, 0, st>>>(b, mask, chains, steps, sink);
+  else if (mlp >= 2) k_probe<WORDS, 2, DEP><<<grid_for(chains), kBlock, 0, st>>>(b, mask, chains, steps, sink);
+  else k_probe<WORDS, 1, DEP><<<grid_for(chains), kBlock, 0, st>>>(b, mask, chains, steps, sink);
 }
 void launch_probe(const uint8_t *buf, uint64_t n_granules_pow2, uint32_t granule, uint64_t chains, uint32_t steps,
-                  uint32_t mlp, unsigned long long *sink, cudaStream_t st) {
+                  uint32_t mlp, bool dependent, unsigned long long *sink, cudaStream_t st) {
   const uint32_t *b = reinterpret_cast<const uint32_t *>(buf);
-  const uint64_t mask = n_granules_pow2 - 1;
-  if (granule == 32) launch_probe_w<8>(b, mask, chains, steps, mlp, sink, st);
-  else if (granule == 64) launch_probe_w<16>(b, mask, chains, steps, mlp, sink, st);
-  else launch_probe_w<32>(b, mask, chains, steps, mlp, sink, st);
+  const uint32_t mask = (uint32_t)(n_granules_pow2 - 1);
+  if (dependent) {
+    if (granule == 32) launch_probe_w<8, true>(b, mask, chains, steps, mlp, sink, st);
+    else if (granule == 64) launch_probe_w<16, true>(b, mask, chains, steps, mlp, sink, st);
+    else launch_probe_w<32, true>(b, mask, chains, steps, mlp, sink, st);
+  } else {
+    if (granule == 32) launch_probe_w<8, false>(b, mask, chains, steps, mlp, sink, st);
+    else if (granule == 64) launch_probe_w<16, false>(b, mask, chains, steps, mlp, sink, st);
+    else launch_probe_w<32, false>(b, mask, chains, steps, mlp, sink, st);
+  }
 }
 
 }  // namespace nm

@@ -18,6 +18,6 @@ void launch_free_generic(const DevIndex &ix, const SegParams &P, bool all, cudaS
 void launch_resolve(const DevIndex &ix, const SegParams &P, cudaStream_t st);
 void launch_checksum(const void *out, int out_width, uint64_t n, unsigned long long *sum, cudaStream_t st);
 void launch_probe(const uint8_t *buf, uint64_t n_granules_pow2, uint32_t granule, uint64_t chains, uint32_t steps,
-                  uint32_t mlp, unsigned long long *sink, cudaStream_t st);
+                  uint32_t mlp, bool dependent, unsigned long long *sink, cudaStream_t st);
 
 }  // namespace nm

@@ -594,9 +594,9 @@ void nm_host_free(void *p) {
 }
 
 int nm_probe_random_access(int device, uint64_t bytes, uint32_t granule, uint64_t chains, uint32_t steps,
-                           uint32_t mlp, double *loads_per_second, float *ms_out) {
+                           uint32_t mlp, int dependent, double *loads_per_second, float *ms_out) {
   if ((granule != 32 && granule != 64 && granule != 128) || bytes < granule || !chains || !steps) return NM_EARG;
-  if (bytes & (bytes - 1)) return NM_EARG;  // power of two
+  if ((bytes & (bytes - 1)) || bytes / granule > 0x100000000ull) return NM_EARG;  // power of two, 32-bit granule index
   NM_CUDA(cudaSetDevice(device));
   uint8_t *buf = nullptr;
   unsigned long long *sink = nullptr;
@@ -609,17 +609,17 @@ int nm_probe_random_access(int device, uint64_t bytes, uint32_t granule, uint64_
     NM_CUDA(cudaEventCreate(&a));
     NM_CUDA(cudaEventCreate(&b));
     const uint64_t ng = bytes / granule;
-    nm::launch_probe(buf, ng, granule, chains, steps < 4 ? steps : 4, mlp, sink, 0);  // warm-up
+    nm::launch_probe(buf, ng, granule, chains, steps < 4 ? steps : 4, mlp, dependent != 0, sink, 0);  // warm-up
     NM_CUDA(cudaDeviceSynchronize());
     NM_CUDA(cudaEventRecord(a, 0));
-    nm::launch_probe(buf, ng, granule, chains, steps, mlp, sink, 0);
+    nm::launch_probe(buf, ng, granule, chains, steps, mlp, dependent != 0, sink, 0);
     NM_CUDA(cudaEventRecord(b, 0));
     NM_CUDA(cudaEventSynchronize(b));
     NM_CUDA(cudaGetLastError());
     float ms = 0;
     NM_CUDA(cudaEventElapsedTime(&ms, a, b));
     if (ms_out) *ms_out = ms;
-    if (loads_per_second) *loads_per_second = (double)chains * steps * (mlp >= 4 ? 4 : mlp >= 2 ? 2 : 1) / (ms * 1e-3);
+    if (loads_per_second) *loads_per_second = (double)chains * steps * (mlp >= 8 ? 8 : mlp >= 4 ? 4 : mlp >= 2 ? 2 : 1) / (ms * 1e-3);
     return NM_OK;
   };
   const int rc = body();

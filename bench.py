@@ -269,6 +269,7 @@ def main():
     pinned_in = []
     for seg, n in segs:
         ws = _lib.Workspace(index, len(seg.data), cuda_stream=stream.cuda_stream)
+        ws.option("ref_lf", 1)
         pb = _lib.PinnedBuffer(len(seg.data))
         pb.array[:] = np.frombuffer(seg.data, dtype=np.uint8)
         ws.upload(pb.ptr, len(seg.data))

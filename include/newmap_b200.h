@@ -116,6 +116,11 @@ int nm_workspace_search(nm_workspace *ws, uint64_t num_kmers, int mode, const ui
                         uint32_t initial_search_length, int use_rc, int algo, int out_width);
 int nm_workspace_download(nm_workspace *ws, void *out);   /* num_kmers * out_width bytes of the last search */
 int nm_workspace_sync(nm_workspace *ws, nm_stats *stats);
+/* Tuning / instrumentation knobs of a workspace; none of them changes a result byte. */
+#define NM_OPT_REF_LF 1   /* 1: also compute stats.ref_lf_steps (LF steps of the reference's trajectory); default 0 */
+#define NM_OPT_DCAP 2     /* first-pass depth cap of the trajectory-free search, characters; 0 = seed length + 12 */
+#define NM_OPT_GSIZE 3    /* positions per certificate group; 0 = 32 */
+int nm_workspace_option(nm_workspace *ws, int option, uint64_t value);
 /* 64-bit FNV-style checksum of the last search's output computed on the device (for
  * device-resident runs that never copy the output back). */
 int nm_workspace_checksum(nm_workspace *ws, uint64_t *sum);

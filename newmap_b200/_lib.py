@@ -54,6 +54,7 @@ SIGNATURES = {
     "nm_workspace_search": (_i, [_vp, _u64, _i, _vp, _u32, _u32, _i, _i, _i]),
     "nm_workspace_download": (_i, [_vp, _vp]),
     "nm_workspace_sync": (_i, [_vp, C.POINTER(Stats)]),
+    "nm_workspace_option": (_i, [_vp, _i, _u64]),
     "nm_workspace_checksum": (_i, [_vp, C.POINTER(_u64)]),
     "nm_host_alloc": (_vp, [_u64]),
     "nm_host_free": (None, [_vp]),
@@ -230,6 +231,11 @@ class Workspace:
             self.close()
         except Exception:
             pass
+
+    def option(self, name: str, value: int):
+        """'ref_lf' | 'dcap' | 'gsize' (NM_OPT_*): instrumentation / tuning, never changes results."""
+        check(load().nm_workspace_option(self._h, {"ref_lf": 1, "dcap": 2, "gsize": 3}[name], int(value)),
+              "nm_workspace_option")
 
     def upload(self, seg_ptr: int, seg_len: int):
         check(load().nm_workspace_upload(self._h, seg_ptr, int(seg_len)), "nm_workspace_upload")

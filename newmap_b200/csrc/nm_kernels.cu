@@ -45,14 +45,88 @@ __global__ void __launch_bounds__(kBlock) k_count(DevIndex ix, const uint8_t *se
   flush_counter(&counters[CTR_LF], steps);
 }
 
-__global__ void __launch_bounds__(kBlock) k_prep(DevIndex ix, SegParams P) {
-  const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
-  if (p < P.seg_len) prep_thread(ix, P, p);
-}
+// prep, fused and vectorised: one thread = 8 consecutive positions, 8 threads = one kTile (64) tile.
+// Writes what prep_thread + nb_tile_thread (nm_core.cuh, kept as the readable definition and for the
+// host-side logic tests) write: codes, packed seed keys (rolling window), next barrier inside the tile,
+// first barrier of the tile.  8-byte / 32-byte stores, tile scan with shuffles.
+constexpr int kPrepV = 8;
+static_assert(kTile == 64 && kPrepV * 8 == (int)kTile, "prep kernel assumes 8 threads x 8 positions per tile");
 
-__global__ void __launch_bounds__(kBlock) k_nb_tile(SegParams P, uint32_t ntiles) {
+__global__ void __launch_bounds__(kBlock) k_prep(DevIndex ix, SegParams P) {
   const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-  if (t < ntiles) nb_tile_thread(P, t);
+  const uint64_t p0 = (uint64_t)t * kPrepV;
+  const uint32_t sl = ix.seed_len;
+  const bool live = p0 < P.seg_len;
+  uint32_t first_barrier = kNoBarrier;
+  unsigned long long cw = 0;  // the thread's 8 codes, one per byte (no dynamically indexed arrays: no local memory)
+  if (live) {
+#pragma unroll
+    for (int j = 0; j < kPrepV; ++j) {
+      const uint8_t cj = (p0 + j < P.seg_len) ? code_of(P, (uint32_t)(p0 + j)) : (uint8_t)kIrregular;
+      cw |= (unsigned long long)cj << (8 * j);
+    }
+    auto code_at = [&](uint32_t j) -> uint32_t {  // code of position p0 + j (beyond the segment: invalidates the window)
+      if (j < kPrepV) return (uint32_t)(cw >> (8 * j)) & 0xFFu;
+      return (p0 + j < P.seg_len) ? (uint32_t)code_of(P, (uint32_t)(p0 + j)) : (uint32_t)kIrregular;
+    };
+    // rolling seed key; `bad` = characters still to shift out before the window is free of irregular /
+    // barrier / out-of-range characters
+    uint32_t key = 0, bad = 0;
+    const uint32_t keymask = (sl >= 16) ? 0xFFFFFFFFu : ((1u << (2 * sl)) - 1u);
+    auto push = [&](uint32_t j) {
+      const uint32_t cj = code_at(j);
+      key = ((key << 2) | (cj & 3u)) & keymask;
+      bad = (p0 + j >= P.seg_len || (cj & (kIrregular | kBarrier))) ? sl : (bad ? bad - 1 : 0);
+    };
+    for (uint32_t j = 0; j + 1 < sl; ++j) push(j);
+    uint32_t keys[kPrepV];
+#pragma unroll
+    for (int i = 0; i < kPrepV; ++i) {
+      push(sl - 1 + i);
+      keys[i] = bad ? kSeedInvalid : key;
+    }
+    if (p0 + kPrepV <= P.seg_len) {
+      *reinterpret_cast<uint2 *>(P.codes + p0) = make_uint2((uint32_t)cw, (uint32_t)(cw >> 32));
+      uint4 *kd = reinterpret_cast<uint4 *>(P.seedkey + p0);
+      kd[0] = make_uint4(keys[0], keys[1], keys[2], keys[3]);
+      kd[1] = make_uint4(keys[4], keys[5], keys[6], keys[7]);
+    } else {
+#pragma unroll
+      for (int j = 0; j < kPrepV; ++j)
+        if (p0 + j < P.seg_len) { P.codes[p0 + j] = (uint8_t)(cw >> (8 * j)); P.seedkey[p0 + j] = keys[j]; }
+    }
+#pragma unroll
+    for (int j = kPrepV - 1; j >= 0; --j)
+      if (p0 + j < P.seg_len && ((cw >> (8 * j)) & kBarrier)) first_barrier = (uint32_t)(p0 + j);
+  }
+  // suffix-min over the 8 lanes of the tile: nearest barrier in the lanes to the right of this one
+  uint32_t right = kNoBarrier, incl = first_barrier;
+#pragma unroll
+  for (int o = 1; o < 8; o <<= 1) {
+    const uint32_t v = __shfl_down_sync(0xffffffffu, incl, o, 8);
+    if ((threadIdx.x & 7) + o < 8) incl = min(incl, v);
+  }
+  {
+    const uint32_t v = __shfl_down_sync(0xffffffffu, incl, 1, 8);
+    if ((threadIdx.x & 7) + 1 < 8) right = v;
+  }
+  if (!live) return;
+  uint32_t next = right, nbv[kPrepV];
+#pragma unroll
+  for (int j = kPrepV - 1; j >= 0; --j) {
+    if (p0 + j < P.seg_len && ((cw >> (8 * j)) & kBarrier)) next = (uint32_t)(p0 + j);
+    nbv[j] = next;
+  }
+  if (p0 + kPrepV <= P.seg_len) {
+    uint4 *nd = reinterpret_cast<uint4 *>(P.nb + p0);
+    nd[0] = make_uint4(nbv[0], nbv[1], nbv[2], nbv[3]);
+    nd[1] = make_uint4(nbv[4], nbv[5], nbv[6], nbv[7]);
+  } else {
+#pragma unroll
+    for (int j = 0; j < kPrepV; ++j)
+      if (p0 + j < P.seg_len) P.nb[p0 + j] = nbv[j];
+  }
+  if ((threadIdx.x & 7) == 0) P.tile_first[p0 / kTile] = incl;
 }
 
 __global__ void __launch_bounds__(kBlock) k_trajectory(DevIndex ix, SegParams P) {
@@ -171,9 +245,7 @@ void launch_count(const DevIndex &ix, const uint8_t *seq, const uint64_t *idx, c
 }
 void launch_prep(const DevIndex &ix, const SegParams &P, cudaStream_t st) {
   if (P.seg_len == 0) return;
-  k_prep<<<grid_for(P.seg_len), kBlock, 0, st>>>(ix, P);
-  const uint32_t ntiles = (P.seg_len + kTile - 1) / kTile;
-  k_nb_tile<<<grid_for(ntiles), kBlock, 0, st>>>(P, ntiles);
+  k_prep<<<grid_for(((uint64_t)P.seg_len + kPrepV - 1) / kPrepV), kBlock, 0, st>>>(ix, P);
 }
 void launch_trajectory(const DevIndex &ix, const SegParams &P, cudaStream_t st) {
   if (P.num_kmers == 0) return;

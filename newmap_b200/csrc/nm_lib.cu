@@ -64,6 +64,7 @@ struct nm_workspace {
   int algo_req = 0, algo_used = 0;
   bool timed_h2d = false, timed_d2h = false;
   void *pending_out = nullptr;
+  uint32_t opt_ref_lf = 0, opt_dcap = 0, opt_gsize = 0;
 };
 
 namespace {
@@ -453,14 +454,12 @@ int nm_workspace_search(nm_workspace *ws, uint64_t num_kmers, int mode, const ui
   P.use_rc = use_rc ? 1 : 0;
   P.out_width = out_width;
   P.fast = 0;
-  P.want_ref_lf = 1;
-  {  // first-pass depth cap: seed + 12 characters unless overridden (tuning knob, results do not depend on it)
-    static const int env_dcap = getenv("NEWMAP_B200_DCAP") ? atoi(getenv("NEWMAP_B200_DCAP")) : 0;
-    static const int env_gs = getenv("NEWMAP_B200_GSIZE") ? atoi(getenv("NEWMAP_B200_GSIZE")) : 0;
+  P.want_ref_lf = ws->opt_ref_lf ? 1 : 0;
+  {
     const uint32_t sl = ws->ix->dev.seed_len;
-    P.dcap = env_dcap > 0 ? (uint32_t)env_dcap : sl + 12;
+    P.dcap = ws->opt_dcap ? ws->opt_dcap : sl + 12;
     if (P.dcap <= sl) P.dcap = sl + 1;
-    P.gsize = env_gs > 0 ? (uint32_t)env_gs : 32;
+    P.gsize = ws->opt_gsize ? ws->opt_gsize : 32;
   }
   ws->algo_req = algo;
   ws->have_search = true;
@@ -543,6 +542,16 @@ int nm_workspace_sync(nm_workspace *ws, nm_stats *stats) {
   return NM_OK;
 }
 
+int nm_workspace_option(nm_workspace *ws, int option, uint64_t value) {
+  if (!ws) return NM_EARG;
+  switch (option) {
+    case NM_OPT_REF_LF: ws->opt_ref_lf = value ? 1u : 0u; return NM_OK;
+    case NM_OPT_DCAP: ws->opt_dcap = (uint32_t)value; return NM_OK;
+    case NM_OPT_GSIZE: if (value > 4096) return NM_EARG; ws->opt_gsize = (uint32_t)value; return NM_OK;
+    default: return NM_EARG;
+  }
+}
+
 int nm_workspace_checksum(nm_workspace *ws, uint64_t *sum) {
   if (!ws || !sum || !ws->have_search) return NM_EARG;
   NM_CUDA(cudaSetDevice(ws->ix->device));
@@ -577,6 +586,7 @@ int nm_min_unique(nm_index *ix, const uint8_t *seg, uint64_t seg_len, uint64_t n
     if (rc != NM_OK) return rc;
   }
   nm_workspace *ws = ix->default_ws;
+  ws->opt_ref_lf = stats ? 1u : 0u;
   int rc = nm_workspace_upload(ws, seg, seg_len);
   if (rc == NM_OK) rc = nm_workspace_search(ws, num_kmers, mode, klist, nk, initial_search_length, use_rc, algo, out_width);
   if (rc == NM_OK) rc = nm_workspace_download(ws, out);

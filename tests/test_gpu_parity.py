@@ -241,3 +241,24 @@ def test_large_segment_properties_and_cross_algorithm_checksum(nm, tmp_path):
         assert ws.checksum() == nm.checksum_host(a)
         ws.close()
         buf.close()
+
+
+def test_tuning_options_do_not_change_results(nm, indexes):
+    ix = indexes("quirk_s6")
+    seq = dict(ora.fasta_records(GOLD / "quirk.fa"))[b"chr1"]
+    kl = list(range(20, 201))
+    want, _ = ix.min_unique(seq, len(seq), kl, True, algo="trajectory")
+    buf = nm.PinnedBuffer(len(seq))
+    buf.array[:] = np.frombuffer(seq, dtype=np.uint8)
+    out = nm.PinnedBuffer(len(seq))
+    ws = nm.Workspace(ix, len(seq))
+    for dcap, gsize in ((0, 0), (7, 1), (8, 5), (13, 64), (40, 200), (1000, 32)):
+        ws.option("dcap", dcap)
+        ws.option("gsize", gsize)
+        ws.upload(buf.ptr, len(seq))
+        ws.search(len(seq), kl, True, out_width=1)
+        ws.download(out.ptr)
+        st = ws.sync()
+        assert st.replayed == 0
+        assert np.array_equal(out.array[:len(seq)], want), (dcap, gsize)
+    ws.close()

@@ -11,7 +11,8 @@ A step = one pass of the hot path over this rank's `segments_per_step` segments.
   value : positions/s with the segments already resident in HBM (CUDA events around K steps)
   e2e   : the same through the C-ABI with pinned HOST buffers, H2D + kernels + D2H every step,
           pipelined over a few workspaces (what newmap_b200.search.write_unique_counts does)
-  roofline : dominant kernel (k_free_fast) -- executed LF steps x 64 B / its CUDA-event time, against
+  roofline : dominant kernel (k_free_chain, pass 1) -- (LF steps x 64 B + seed lookups x 32 B) / its CUDA-event time
+          measured with one search on the GPU at a time, against
           the measured streaming HBM peak (MEASURED_PEAKS.json) and against a random 32 B-sector
           probe measured in the same run
   cpu_baseline / --impl reference : the reference's own AVX2/OpenMP count code (oracle/_ref) under
@@ -260,7 +261,10 @@ def main():
     t0 = time.time()
     index = _lib.Index(ix_path, device=local)
     log(f"[bench r{rank}] index resident in {time.time() - t0:.1f}s: bwt {index.bwt_length}, "
-        f"{index.info.device_bytes / 1e9:.2f} GB HBM; {S} of {total_segments} segments per step")
+        f"{index.info.device_bytes / 1e9:.2f} GB HBM (derived seed table depth {index.derived_seed_length}); "
+        f"{S} of {total_segments} segments per step")
+    base["config"]["index"] += (f"; derived on the device at load: rank32 layout, seed table of depth "
+                                f"{index.derived_seed_length} ({index.info.device_bytes / 1e9:.1f} GB HBM in all)")
     positions_per_step = sum(n for _, n in segs)
     max_len = max(len(s.data) for s, _ in segs)
     stream = torch.cuda.current_stream()
@@ -270,7 +274,6 @@ def main():
     pinned_in = []
     for seg, n in segs:
         ws = _lib.Workspace(index, len(seg.data), cuda_stream=stream.cuda_stream)
-        ws.option("ref_lf", 1)
         pb = _lib.PinnedBuffer(len(seg.data))
         pb.array[:] = np.frombuffer(seg.data, dtype=np.uint8)
         ws.upload(pb.ptr, len(seg.data))
@@ -342,6 +345,15 @@ def main():
     ms_e2e = (time.perf_counter() - t0) * 1e3
     barrier()
 
+    # ---- the same searches one at a time (nothing else on the GPU): per-kernel CUDA-event times for the roofline.
+    # In the timed regions above the segments' kernels overlap across streams, so their event times are not
+    # durations of a kernel that has the GPU to itself.
+    iso: list = []
+    for _ in range(args.steps):
+        for ws, n in resident:
+            ws.search(n, kl, True, algo=args.algo, out_width=1)
+            iso.append(ws.sync().as_dict())
+
     # ---- cross-check one segment against the reference-trajectory kernel (different algorithm, same bytes)
     ws0, n0 = resident[0]
     ws0.search(n0, kl, True, algo="trajectory", out_width=1)
@@ -361,10 +373,19 @@ def main():
         positions_all = float(positions_per_step)
 
     if rank == 0:
-        lf = sum(s["lf_steps"] for s in stats)
-        ms_search = sum(s["ms_search"] for s in stats)
-        launches = len(stats)
-        ref_lf = sum(s["ref_lf_steps"] for s in stats)
+        lf = sum(s["lf_steps"] for s in iso)
+        ms_search = sum(s["ms_search"] for s in iso)
+        launches = len(iso)
+        lf1 = sum(s["lf_steps_pass1"] for s in iso)
+        seeds = sum(s["seed_lookups"] for s in iso)
+        seeds1 = sum(s["seed_lookups_pass1"] for s in iso)
+        ms_pass1 = sum(s["ms_pass1"] for s in iso)
+        bytes1 = lf1 * 64 + seeds1 * 32
+        bytes_all = lf * 64 + seeds * 32
+        traffic = None
+        tf = ROOT / "profiles" / "traffic.json"     # dram__bytes_read+write per launch from an `ncu --set full` capture
+        if tf.is_file():
+            traffic = json.loads(tf.read_text()).get(args.workload, {}).get("k_free_chain_pass1")
         peaks = {}
         pk = ROOT / "MEASURED_PEAKS.json"
         if pk.is_file():
@@ -378,7 +399,7 @@ def main():
                            _lib.probe_random_access(local, 2 << 30, g, 2 << 20, 32, 4, True)[0])
             probe_indep[g] = max(_lib.probe_random_access(local, 2 << 30, g, 2 << 20, 32, 8, False)[0],
                                  _lib.probe_random_access(local, 2 << 30, g, 8 << 20, 32, 4, False)[0])
-        achieved = lf * 64 / (ms_search * 1e-3) / 1e9 if ms_search else None
+        achieved = bytes1 / (ms_pass1 * 1e-3) / 1e9 if ms_pass1 else None
         line = dict(base)
         line.update({
             "value": positions_all * args.steps / (ms_value * 1e-3),
@@ -387,22 +408,32 @@ def main():
                     "h2d_bytes_per_step": int(sum(len(s.data) for s, _ in segs)),
                     "d2h_bytes_per_step": int(positions_per_step), "ms_per_step": ms_e2e / args.steps,
                     "timing": "host clock bracketed by device synchronize; 3 pipelined workspaces"},
-            "gpu_launches": 6 * launches,
+            "gpu_launches": int(sum(s["launches"] for s in stats)),
             "clocks": clocks.summary(),
-            "roofline": {"bound": "hbm", "kernel": "k_free_fast", "achieved": achieved, "peak": hbm_peak,
+            "roofline": {"bound": "hbm", "kernel": "k_free_chain (pass 1: every position, depth-capped)",
+                         "achieved": achieved, "peak": hbm_peak,
                          "unit": "GB/s", "frac": (achieved / hbm_peak) if achieved else None, "peak_source": peak_src,
-                         "traffic": None,
-                         "algorithmic_bytes_per_unit": "64 B per LF step (2 rank queries x one 32 B sector)",
-                         "lf_steps_per_launch": lf / max(1, launches), "ms_per_launch": ms_search / max(1, launches),
-                         "lf_steps_per_position": lf / max(1, positions_per_step * args.steps),
-                         "ref_trajectory_lf_steps_per_position": ref_lf / max(1, positions_per_step * args.steps),
+                         "traffic": traffic,
+                         "algorithmic_bytes_per_unit": "64 B per LF step (2 rank queries x one 32 B sector) + 32 B per "
+                                                       "seed-table lookup (one sector)",
+                         "algorithmic_bytes_per_launch": bytes1 / max(1, launches),
+                         "lf_steps_per_launch": lf1 / max(1, launches), "seed_lookups_per_launch": seeds1 / max(1, launches),
+                         "ms_per_launch": ms_pass1 / max(1, launches),
+                         "timing": "CUDA events on the workspace stream, one search at a time (no overlap)",
+                         "whole_search": {"kernels": "k_free_chain pass 1 + k_free_cert + k_free_chain pass 3",
+                                          "achieved": bytes_all / (ms_search * 1e-3) / 1e9 if ms_search else None,
+                                          "ms_per_segment": ms_search / max(1, launches),
+                                          "lf_steps_per_position": lf / max(1, positions_per_step * args.steps),
+                                          "seed_lookups_per_position": seeds / max(1, positions_per_step * args.steps)},
+                         "seed_depth": iso[0]["seed_depth"] if iso else None,
+                         "ref_trajectory_lf_steps_per_position": st_traj.lf_steps / max(1, n0),
                          "random_sector_probe": {"dependent_loads_per_s": probe, "independent_loads_per_s": probe_indep,
                                                  "gbs_32B_independent": probe_indep[32] * 32 / 1e9,
                                                  "how": "2 GiB buffer; best of {8 Mi threads x 1, 2 Mi x 4} dependent chains "
                                                         "and {2 Mi x 8, 8 Mi x 4} independent loads, 32 steps"},
-                         "frac_random_sector": (lf * 2 / (ms_search * 1e-3) / probe_indep[32]) if ms_search else None},
-            "kernel_ms": {k: sum(s[k] for s in stats) / max(1, launches) for k in
-                          ("ms_prep", "ms_search", "ms_generic", "ms_resolve")},
+                         "frac_random_sector": ((bytes1 / 32) / (ms_pass1 * 1e-3) / probe_indep[32]) if ms_pass1 else None},
+            "kernel_ms": {k: sum(s[k] for s in iso) / max(1, launches) for k in
+                          ("ms_prep", "ms_pass1", "ms_cert", "ms_pass3", "ms_generic", "ms_resolve")},
             "trajectory_kernel": {"positions": n0, "ms": st_traj.ms_search, "lf_steps": st_traj.lf_steps,
                                   "queries": st_traj.queries, "positions_per_s": n0 / (st_traj.ms_search * 1e-3)},
         })

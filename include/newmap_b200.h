@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define NM_ABI_VERSION 1
+#define NM_ABI_VERSION 2
 
 /* error codes (negative = failure, mirroring enum AwFmReturnCode's sign convention,
  * AvxWindowFmIndex/src/AwFmIndex.h:131-137) */
@@ -60,6 +60,8 @@ typedef struct nm_index_info {
   uint32_t sa_compression_ratio;
   uint32_t has_rank32;      /* 1 when the 32-byte rank layout was built (bwt_length < 2^32-1) */
   int32_t device;
+  uint32_t derived_seed_length; /* depth of the deeper seed table derived on the device, 0 = none */
+  uint32_t reserved;
 } nm_index_info;
 
 typedef struct nm_stats {
@@ -67,13 +69,23 @@ typedef struct nm_stats {
   uint64_t lf_steps;          /* backward-extension steps executed on the device */
   uint64_t queries;           /* (position,length) count queries executed (trajectory algo) */
   uint64_t generic_searches;  /* searches routed to the unmodified-layout kernel (x letters, exceptions ...) */
-  uint64_t ref_lf_steps;      /* LF steps the reference's trajectory would have executed (0 if not computed) */
+  uint64_t ref_lf_steps;      /* LF steps the reference's trajectory would have executed (0 if not computed: it
+                                 needs the search to start from the file's own seed table -- NM_OPT_REF_LF forces
+                                 that; nm_min_unique fills it only when the derived table is not in use) */
   int64_t zero_pos;           /* first (round, position) whose two-strand count was 0, else -1 */
   int64_t zero_len;
   int64_t zero_round;
   uint32_t algo_used;         /* NM_ALGO_* that produced the output */
   uint32_t replayed;          /* 1 if NM_ALGO_AUTO fell back to the trajectory replay */
   float ms_h2d, ms_prep, ms_search, ms_generic, ms_resolve, ms_d2h, ms_total; /* CUDA-event times of this call */
+  /* trajectory-free search, pass by pass (ms_search = ms_pass1 + ms_cert + ms_pass3) */
+  float ms_pass1, ms_cert, ms_pass3;
+  uint32_t launches;          /* kernels launched for this call */
+  uint32_t seed_depth;        /* depth of the seed table the chains started from */
+  uint32_t reserved;
+  uint64_t lf_steps_pass1;    /* part of lf_steps executed by the first pass (every position, depth-capped) */
+  uint64_t seed_lookups;      /* seed-table lookups of the trajectory-free search */
+  uint64_t seed_lookups_pass1;
 } nm_stats;
 
 int nm_abi_version(void);
@@ -87,6 +99,13 @@ int nm_device_count(void);              /* >= 0, or NM_ECUDA */
 int nm_index_open(const char *path, int device, nm_index **out);
 void nm_index_close(nm_index *ix);
 int nm_index_info_get(const nm_index *ix, nm_index_info *info);
+/* The seed table of the file (AwFmKmerTable.c:24-35, depth kmerLengthInSeedTable, 12 by default) saves the
+ * first seedLen backward-extension steps of a query.  With 180 GB of HBM a DEEPER table pays: nm_index_open
+ * derives one on the device from the file's table and the BWT (one extension step per entry and level; depth
+ * chosen from bwtLength and free memory, at most 16 = 34 GB; NEWMAP_B200_SEED_DEPTH overrides, 0 = none) and
+ * searches whose shortest length reaches that depth start their chains from it.  This call rebuilds it at
+ * another depth (<= seed length: drop it).  No search may be in flight.  Results never depend on it. */
+int nm_index_set_seed_depth(nm_index *ix, uint32_t depth);
 
 /* counts[q] = occurrences of seq[idx[q] : idx[q]+len[q]] in the indexed text (u32, five-letter
  * alphabet a c g t/u x exactly like AwFmParallelSearch.c:136-255).  reverse_complement != 0
@@ -117,9 +136,13 @@ int nm_workspace_search(nm_workspace *ws, uint64_t num_kmers, int mode, const ui
 int nm_workspace_download(nm_workspace *ws, void *out);   /* num_kmers * out_width bytes of the last search */
 int nm_workspace_sync(nm_workspace *ws, nm_stats *stats);
 /* Tuning / instrumentation knobs of a workspace; none of them changes a result byte. */
-#define NM_OPT_REF_LF 1   /* 1: also compute stats.ref_lf_steps (LF steps of the reference's trajectory); default 0 */
-#define NM_OPT_DCAP 2     /* first-pass depth cap of the trajectory-free search, characters; 0 = seed length + 12 */
+#define NM_OPT_REF_LF 1   /* 1: also compute stats.ref_lf_steps (LF steps of the reference's trajectory) and, for that,
+                             start the chains from the file's seed table instead of the derived one; default 0 */
+#define NM_OPT_DCAP 2     /* first-pass depth cap of the trajectory-free search, characters; 0 = seed depth in use + 8 (derived
+                             table) or + 12 (the file's table) */
 #define NM_OPT_GSIZE 3    /* positions per certificate group; 0 = 32 */
+#define NM_OPT_PASS1 4    /* kernel of the first pass: 0 = chosen from the seed depth in use (default), 1 = one thread per
+                             position, 2 = tiled (seed lookups batched, lanes refilled from a queue) */
 int nm_workspace_option(nm_workspace *ws, int option, uint64_t value);
 /* 64-bit FNV-style checksum of the last search's output computed on the device (for
  * device-resident runs that never copy the output back). */

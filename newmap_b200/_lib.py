@@ -22,7 +22,8 @@ NM_EOPEN, NM_EFORMAT, NM_EVERSION, NM_EALLOC, NM_ESHORT, NM_EARG, NM_ECUDA, NM_E
 class IndexInfo(C.Structure):
     _fields_ = [("bwt_length", C.c_uint64), ("n_blocks", C.c_uint64), ("prefix_sums", C.c_uint64 * 6),
                 ("device_bytes", C.c_uint64), ("seed_length", C.c_uint32), ("sa_compression_ratio", C.c_uint32),
-                ("has_rank32", C.c_uint32), ("device", C.c_int32)]
+                ("has_rank32", C.c_uint32), ("device", C.c_int32), ("derived_seed_length", C.c_uint32),
+                ("reserved", C.c_uint32)]
 
 
 class Stats(C.Structure):
@@ -30,7 +31,10 @@ class Stats(C.Structure):
                 ("generic_searches", C.c_uint64), ("ref_lf_steps", C.c_uint64), ("zero_pos", C.c_int64),
                 ("zero_len", C.c_int64), ("zero_round", C.c_int64), ("algo_used", C.c_uint32),
                 ("replayed", C.c_uint32), ("ms_h2d", C.c_float), ("ms_prep", C.c_float), ("ms_search", C.c_float),
-                ("ms_generic", C.c_float), ("ms_resolve", C.c_float), ("ms_d2h", C.c_float), ("ms_total", C.c_float)]
+                ("ms_generic", C.c_float), ("ms_resolve", C.c_float), ("ms_d2h", C.c_float), ("ms_total", C.c_float),
+                ("ms_pass1", C.c_float), ("ms_cert", C.c_float), ("ms_pass3", C.c_float), ("launches", C.c_uint32),
+                ("seed_depth", C.c_uint32), ("reserved", C.c_uint32), ("lf_steps_pass1", C.c_uint64),
+                ("seed_lookups", C.c_uint64), ("seed_lookups_pass1", C.c_uint64)]
 
     def as_dict(self) -> dict:
         return {name: getattr(self, name) for name, _ in self._fields_}
@@ -46,6 +50,7 @@ SIGNATURES = {
     "nm_index_open": (_i, [C.c_char_p, _i, C.POINTER(_vp)]),
     "nm_index_close": (None, [_vp]),
     "nm_index_info_get": (_i, [_vp, C.POINTER(IndexInfo)]),
+    "nm_index_set_seed_depth": (_i, [_vp, _u32]),
     "nm_count_from_sequence": (_i, [_vp, _vp, _u64, _vp, _vp, _u64, _i, _vp, C.POINTER(_u64)]),
     "nm_min_unique": (_i, [_vp, _vp, _u64, _u64, _i, _vp, _u32, _u32, _i, _i, _i, _vp, C.POINTER(Stats)]),
     "nm_workspace_create": (_i, [_vp, _u64, _vp, C.POINTER(_vp)]),
@@ -77,7 +82,7 @@ def load() -> C.CDLL:
         for name, (res, args) in SIGNATURES.items():
             fn = getattr(L, name)
             fn.restype, fn.argtypes = res, args
-        if L.nm_abi_version() != 1:
+        if L.nm_abi_version() != 2:
             raise ImportError("libnewmap_b200.so ABI version mismatch")
         _lib = L
     return _lib
@@ -163,6 +168,17 @@ class Index:
         return int(self.info.seed_length)
 
     @property
+    def derived_seed_length(self) -> int:
+        """Depth of the deeper seed table derived on the device at load time (0 = none)."""
+        return int(self.info.derived_seed_length)
+
+    def set_seed_depth(self, depth: int) -> None:
+        """Rebuild the derived seed table at `depth` letters (<= seed_length drops it).  Speed only."""
+        L = load()
+        check(L.nm_index_set_seed_depth(self._h, int(depth)), "nm_index_set_seed_depth")
+        check(L.nm_index_info_get(self._h, C.byref(self.info)), "nm_index_info_get")
+
+    @property
     def bwt_length(self) -> int:
         return int(self.info.bwt_length)
 
@@ -233,8 +249,8 @@ class Workspace:
             pass
 
     def option(self, name: str, value: int):
-        """'ref_lf' | 'dcap' | 'gsize' (NM_OPT_*): instrumentation / tuning, never changes results."""
-        check(load().nm_workspace_option(self._h, {"ref_lf": 1, "dcap": 2, "gsize": 3}[name], int(value)),
+        """'ref_lf' | 'dcap' | 'gsize' | 'pass1' (NM_OPT_*): instrumentation / tuning, never changes results."""
+        check(load().nm_workspace_option(self._h, {"ref_lf": 1, "dcap": 2, "gsize": 3, "pass1": 4}[name], int(value)),
               "nm_workspace_option")
 
     def upload(self, seg_ptr: int, seg_len: int):

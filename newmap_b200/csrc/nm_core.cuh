@@ -100,19 +100,24 @@ constexpr uint8_t kLetterMask = 0x07;  // 0..3 = a c g t/u, 4 = anything else ("
 constexpr uint8_t kIrregular = 0x08;   // letter x, or U/u (complemented differently by search.py:22): generic kernel only
 constexpr uint8_t kBarrier = 0x10;     // no queried k-mer may contain this position
 constexpr uint8_t kNoStart = 0x20;     // search.py:23,744-766: start byte not in b'ACGTactg'
+constexpr uint8_t kSeedBad = 0x40;     // the window of P.sl letters starting here holds an irregular letter, a barrier or
+                                       // the segment end: seedkey[p] is not a seed-table key
 
 constexpr uint32_t kNone = 0u;               // G: no unique suffix within bounds
 constexpr uint32_t kInf = 0xFFFFFFFFu;       // R: other strand still present at the longest length
 constexpr uint32_t kPending = 0xFFFFFFFEu;   // G/R: to be computed by the generic kernel
 constexpr uint32_t kDeep = 0xFFFFFFFDu;      // G/R: undecided at the depth cap of the first pass
-constexpr uint32_t kSeedInvalid = 0xFFFFFFFFu;
 constexpr uint32_t kNoBarrier = 0xFFFFFFFFu;
 constexpr uint32_t kTile = 64;               // nb[] tile (positions per thread of nb_tile_thread)
 
 // counters[] slots
-enum { CTR_LF = 0, CTR_QUERIES = 1, CTR_GENERIC = 2, CTR_ANOMALY = 3, CTR_ZERO_KEY = 4, CTR_REF_LF = 5, CTR_N = 8 };
+enum { CTR_LF = 0, CTR_QUERIES = 1, CTR_GENERIC = 2, CTR_ANOMALY = 3, CTR_ZERO_KEY = 4, CTR_REF_LF = 5,
+       CTR_LF_PASS1 = 6,  // LF steps of the first (depth-capped, every position) pass of the trajectory-free search
+       CTR_SEEDS = 7,     // seed-table lookups of the trajectory-free search (one 32-byte sector each)
+       CTR_SEEDS_PASS1 = 8,  // the part of CTR_SEEDS looked up by the first pass
+       CTR_N = 16 };
 
-struct SeedEntry32 {
+struct alignas(8) SeedEntry32 {  // one 64-bit load
   uint32_t start, len;
 };
 
@@ -121,6 +126,8 @@ struct DevIndex {
   const uint32_t *rank32;     // (n64 + 1) * 8 u32, or nullptr
   const SeedEntry32 *seed32;  // 4^seed_len entries, or nullptr
   const uint64_t *seed64;     // 4^seed_len {start,end} pairs exactly as in the file
+  const SeedEntry32 *seedx;   // derived on the device at load time: 4^seedx_len entries of a DEEPER seed table
+  uint32_t seedx_len;         // (seed_len < seedx_len <= 16), or nullptr / 0
   const uint32_t *c32;        // prefixSums as u32[6] in device memory (rank32 path), or nullptr
   uint64_t C[6];              // prefixSums, AwFmCreate.c:299-305
   uint64_t bwt_len;
@@ -324,7 +331,9 @@ NM_HD uint32_t count_both(const DevIndex &ix, const uint8_t *seg, uint64_t i, ui
 struct SegParams {
   const uint8_t *seg;    // raw bytes, seg_len
   uint8_t *codes;        // seg_len
-  uint32_t *seedkey;     // seg_len: packed seed_len letters starting at p, or kSeedInvalid
+  uint32_t *seedkey;     // seg_len: the sl letters starting at p packed 2 bits each (valid unless codes[p] & kSeedBad)
+  const SeedEntry32 *seedtab;  // seed table the chains start from: 4^sl entries (index seed table or the deeper one)
+  uint32_t sl;           // its depth; kmin >= sl
   uint32_t *nb;          // seg_len: position of the first barrier >= p inside p's tile, or kNoBarrier
   uint32_t *tile_first;  // ceil(seg_len / kTile): first barrier of the tile, or kNoBarrier
   uint32_t *G;           // seg_len + 1: length of the shortest unique suffix ending at e (forward strand)
@@ -439,10 +448,10 @@ NM_HD uint8_t code_of(const SegParams &P, uint32_t p) {
 }
 
 NM_HD void prep_thread(const DevIndex &ix, const SegParams &P, uint32_t p) {
+  (void)ix;
   const uint8_t c0 = code_of(P, p);
-  P.codes[p] = c0;
   uint32_t key = 0;
-  const uint32_t sl = ix.seed_len;
+  const uint32_t sl = P.sl;
   bool ok = (uint64_t)p + sl <= P.seg_len;
   if (ok) {
     for (uint32_t j = 0; j < sl; ++j) {
@@ -451,7 +460,8 @@ NM_HD void prep_thread(const DevIndex &ix, const SegParams &P, uint32_t p) {
       key = (key << 2) | (c & 3u);
     }
   }
-  P.seedkey[p] = ok ? key : kSeedInvalid;
+  P.codes[p] = ok ? c0 : (uint8_t)(c0 | kSeedBad);
+  P.seedkey[p] = ok ? key : 0u;
 }
 
 // one thread per tile of kTile positions: nb[p] = first barrier at or after p inside the tile
@@ -470,12 +480,18 @@ NM_HD void nb_tile_thread(const SegParams &P, uint32_t t) {
 // seed key of the other strand's k-mer starting (in search order) at i: letters 3-c[i], 3-c[i+1], ...
 // with c[i] LEAST significant (it is the last character of the reverse-complemented k-mer)
 NM_HD uint32_t rc_seed_key(uint32_t fwdkey, uint32_t sl) {
-  uint32_t r = 0;
-  for (uint32_t j = 0; j < sl; ++j) {
-    r = (r << 2) | (3u - (fwdkey & 3u));
-    fwdkey >>= 2;
-  }
-  return r;
+  uint32_t x = ~fwdkey;  // 3 - c == ~c on two bits
+#if defined(__CUDA_ARCH__)
+  x = __brev(x);
+#else
+  x = ((x >> 1) & 0x55555555u) | ((x & 0x55555555u) << 1);
+  x = ((x >> 2) & 0x33333333u) | ((x & 0x33333333u) << 2);
+  x = ((x >> 4) & 0x0F0F0F0Fu) | ((x & 0x0F0F0F0Fu) << 4);
+  x = ((x >> 8) & 0x00FF00FFu) | ((x & 0x00FF00FFu) << 8);
+  x = (x >> 16) | (x << 16);
+#endif
+  x = ((x >> 1) & 0x55555555u) | ((x & 0x55555555u) << 1);  // bit reversal also swapped the two bits of a letter
+  return x >> (32u - 2u * sl);                              // the sl letters now sit at the top
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -502,85 +518,91 @@ struct ChainResult {
   bool wall;        // stopped because the next character is a barrier or beyond the segment
 };
 
-// forward strand: extend leftwards from end e (pattern seg[e-d, e)), stop when count == 1
-NM_HD ChainResult run_fwd_chain(const DevIndex &ix, const uint32_t *C32, const SegParams &P, uint32_t e,
-                                uint32_t maxdepth, uint32_t &steps) {
-  const uint32_t sl = ix.seed_len;
-  ChainResult r{0, 0, false};
+// A chain = one backward search, kept as {half-open SA interval, depth}.  kind 0: forward strand, pattern
+// seg[p-d, p) extended leftwards from end p, stops when count == 1.  kind 1: other strand, pattern
+// rc(seg[p, p+d)) extended rightwards from start p, stops when count == 0.
+struct ChainState {
   uint32_t lo, hi, d;
-  uint32_t key = kSeedInvalid;
-  if (e >= sl && !(P.mode == 1 && e == P.seg_len)) key = P.seedkey[e - sl];
-  if (key != kSeedInvalid) {
-    const SeedEntry32 s = ix.seed32[key];
-    lo = s.start;
-    hi = s.start + s.len;
-    d = sl;
-  } else {  // from depth 1 (the caller has checked that seg[e-1] is not a barrier)
-    const unsigned l = P.codes[e - 1] & kLetterMask;
-    lo = C32[l];
-    hi = C32[l + 1];
-    d = 1;
-  }
-  for (;;) {
-    const uint32_t n = hi - lo;
-    if (n <= 1u) {
-      if (n == 1u) r.d_hit = d;
-      else atomic_or64(&P.counters[CTR_ANOMALY], 1ull);  // a substring of the segment is absent from the index
-      r.d_stop = d;
-      return r;
-    }
-    if (d >= e) { r.wall = true; break; }
-    const uint8_t c = P.codes[e - 1 - d];
-    if (c & kBarrier) { r.wall = true; break; }
-    if (d >= maxdepth) break;
-    lf_fast(ix, C32, c & kLetterMask, lo, hi);
-    ++d;
-    ++steps;
-  }
-  r.d_stop = d;
-  return r;
-}
+};
 
+// where the chain starts: the seed table at depth P.sl when the window of P.sl letters is clean, else depth 1
+// (the caller has checked fwd_wanted / rc_wanted)
+NM_HD bool chain_seeded(const SegParams &P, uint32_t kind, uint32_t p) {
+  if (kind == 0u) return p >= P.sl && !(P.mode == 1 && p == P.seg_len) && !(P.codes[p - P.sl] & kSeedBad);
+  return !(P.codes[p] & kSeedBad);
+}
+NM_HD uint32_t chain_seed_key(const SegParams &P, uint32_t kind, uint32_t p) {
+  return kind == 0u ? P.seedkey[p - P.sl] : rc_seed_key(P.seedkey[p], P.sl);
+}
 NM_HD unsigned rc_letter_of_code(uint8_t c) {
   const unsigned l = c & kLetterMask;
   if (c & kIrregular) return l == 3u ? 3u : 4u;  // U/u keeps letter t (search.py:22 does not complement it)
   return 3u - l;
 }
+NM_HD ChainState chain_from_seed(const SeedEntry32 s, uint32_t sl) { return ChainState{s.start, s.start + s.len, sl}; }
+NM_HD ChainState chain_from_letter(const uint32_t *C32, const SegParams &P, uint32_t kind, uint32_t p) {
+  const unsigned l = kind == 0u ? (unsigned)(P.codes[p - 1] & kLetterMask) : rc_letter_of_code(P.codes[p]);
+  return ChainState{C32[l], C32[l + 1], 1u};
+}
+NM_HD ChainState chain_init(const uint32_t *C32, const SegParams &P, uint32_t kind, uint32_t p, uint32_t &seeds) {
+  if (chain_seeded(P, kind, p)) {
+    ++seeds;
+    return chain_from_seed(P.seedtab[chain_seed_key(P, kind, p)], P.sl);
+  }
+  return chain_from_letter(C32, P, kind, p);
+}
 
-// other strand: extend rightwards from start i (pattern rc(seg[i, i+d))), stop when count == 0
-NM_HD ChainResult run_rc_chain(const DevIndex &ix, const uint32_t *C32, const SegParams &P, uint32_t i,
-                               uint32_t maxdepth, uint32_t &steps) {
-  const uint32_t sl = ix.seed_len;
+// the chain's own stop condition at its present depth (no memory access)
+NM_HD bool chain_finished(const SegParams &P, uint32_t kind, const ChainState &s, ChainResult &r) {
+  const uint32_t n = s.hi - s.lo;
+  if (kind == 0u ? n > 1u : n != 0u) return false;
+  r.d_hit = (kind == 0u && n == 0u) ? 0u : s.d;
+  if (kind == 0u && n == 0u) atomic_or64(&P.counters[CTR_ANOMALY], 1ull);  // a substring of the segment is absent from the index
+  r.d_stop = s.d;
+  r.wall = false;
+  return true;
+}
+
+// One iteration of a chain: either it ends here (returns true, r filled) or it takes one backward-extension
+// step.  Written once for both kinds so that the lanes of a warp that hold chains of either kind stay converged.
+NM_HD bool chain_iterate(const DevIndex &ix, const uint32_t *C32, const SegParams &P, uint32_t kind, uint32_t p,
+                         ChainState &s, uint32_t maxdepth, uint32_t &steps, ChainResult &r) {
+  if (chain_finished(P, kind, s, r)) return true;
+  r.d_hit = 0;
+  r.d_stop = s.d;
+  const bool edge = kind == 0u ? s.d >= p : p + s.d >= P.seg_len;
+  if (edge) { r.wall = true; return true; }
+  const uint8_t c = P.codes[kind == 0u ? p - 1u - s.d : p + s.d];
+  if (c & kBarrier) { r.wall = true; return true; }
+  r.wall = false;
+  if (s.d >= maxdepth) return true;
+  lf_fast(ix, C32, kind == 0u ? (unsigned)(c & kLetterMask) : rc_letter_of_code(c), s.lo, s.hi);
+  ++s.d;
+  ++steps;
+  return false;
+}
+
+NM_HD ChainResult run_chain(const DevIndex &ix, const uint32_t *C32, const SegParams &P, uint32_t kind, uint32_t p,
+                            uint32_t maxdepth, uint32_t &steps, uint32_t &seeds) {
+  ChainState s = chain_init(C32, P, kind, p, seeds);
   ChainResult r{0, 0, false};
-  uint32_t lo, hi, d;
-  const uint32_t key = P.seedkey[i];
-  if (key != kSeedInvalid) {
-    const SeedEntry32 s = ix.seed32[rc_seed_key(key, sl)];
-    lo = s.start;
-    hi = s.start + s.len;
-    d = sl;
-  } else {  // from depth 1 (the caller has checked that seg[i] may start a k-mer)
-    const unsigned l = rc_letter_of_code(P.codes[i]);
-    lo = C32[l];
-    hi = C32[l + 1];
-    d = 1;
-  }
-  for (;;) {
-    if (hi == lo) {
-      r.d_hit = d;
-      r.d_stop = d;
-      return r;
-    }
-    if (i + d >= P.seg_len) { r.wall = true; break; }
-    const uint8_t c = P.codes[i + d];
-    if (c & kBarrier) { r.wall = true; break; }
-    if (d >= maxdepth) break;
-    lf_fast(ix, C32, rc_letter_of_code(c), lo, hi);
-    ++d;
-    ++steps;
-  }
-  r.d_stop = d;
+  while (!chain_iterate(ix, C32, P, kind, p, s, maxdepth, steps, r)) {}
   return r;
+}
+NM_HD ChainResult run_fwd_chain(const DevIndex &ix, const uint32_t *C32, const SegParams &P, uint32_t e,
+                                uint32_t maxdepth, uint32_t &steps, uint32_t &seeds) {
+  return run_chain(ix, C32, P, 0u, e, maxdepth, steps, seeds);
+}
+NM_HD ChainResult run_rc_chain(const DevIndex &ix, const uint32_t *C32, const SegParams &P, uint32_t i,
+                               uint32_t maxdepth, uint32_t &steps, uint32_t &seeds) {
+  return run_chain(ix, C32, P, 1u, i, maxdepth, steps, seeds);
+}
+
+// value stored in G (none = kNone) / R (none = kInf) for a finished chain of a pass capped at `cap`
+NM_HD uint32_t chain_value(const SegParams &P, const ChainResult &r, uint32_t cap, uint32_t none) {
+  if (r.d_hit) return r.d_hit;
+  if (!r.wall && r.d_stop < P.kmax && r.d_stop >= cap) return kDeep;
+  return none;
 }
 
 NM_HD bool fwd_wanted(const SegParams &P, uint32_t e) { return e >= 1 && !(P.codes[e - 1] & kBarrier); }
@@ -590,33 +612,32 @@ NM_HD bool rc_wanted(const SegParams &P, uint32_t i) {
 
 // pass 1 and pass 3 share this: `cap` = P.dcap in pass 1, kmax in pass 3 (which only redoes kDeep entries)
 NM_HD void free_chain_thread(const DevIndex &ix, const uint32_t *C32, const SegParams &P, uint32_t p, bool first,
-                             uint32_t &steps) {
+                             uint32_t &steps, uint32_t &seeds) {
   const uint32_t cap = first ? (P.dcap < P.kmax ? P.dcap : P.kmax) : P.kmax;
   if (first || P.G[p] == kDeep) {
     uint32_t g = kNone;
     if (fwd_wanted(P, p)) {
-      const ChainResult r = run_fwd_chain(ix, C32, P, p, cap, steps);
-      if (r.d_hit) g = r.d_hit;
-      else if (!r.wall && r.d_stop < P.kmax && r.d_stop >= cap) g = kDeep;
+      g = chain_value(P, run_fwd_chain(ix, C32, P, p, cap, steps, seeds), cap, kNone);
     }
     P.G[p] = g;
   }
   if (p < P.seg_len && (first || P.R[p] == kDeep)) {
     uint32_t rr = kInf;
     if (rc_wanted(P, p)) {
-      const ChainResult r = run_rc_chain(ix, C32, P, p, cap, steps);
-      if (r.d_hit) rr = r.d_hit;
-      else if (!r.wall && r.d_stop < P.kmax && r.d_stop >= cap) rr = kDeep;
+      rr = chain_value(P, run_rc_chain(ix, C32, P, p, cap, steps, seeds), cap, kInf);
     }
     P.R[p] = rr;
   }
 }
 
 // pass 2: group t covers ends e in (t*gs, (t+1)*gs] and starts i in [t*gs, (t+1)*gs)
-NM_HD void free_cert_thread(const DevIndex &ix, const uint32_t *C32, const SegParams &P, uint32_t t, uint32_t &steps) {
+// (parts: bit 0 = the forward-strand half, bit 1 = the other-strand half; the kernel gives each half its own thread
+// so that the two long chains of a group run side by side)
+NM_HD void free_cert_thread(const DevIndex &ix, const uint32_t *C32, const SegParams &P, uint32_t t, uint32_t &steps,
+                            uint32_t &seeds, uint32_t parts = 3u) {
   const uint32_t gs = P.gsize;
   // ---- forward strand: chain from the LARGEST deep end e0; it contains seg[e'-L, e') for every smaller e'
-  {
+  if (parts & 1u) {
     const uint32_t first = t * gs + 1;
     uint32_t last = first + gs - 1;
     if (last > P.seg_len) last = P.seg_len;
@@ -624,7 +645,7 @@ NM_HD void free_cert_thread(const DevIndex &ix, const uint32_t *C32, const SegPa
     for (uint32_t e = first; e <= last; ++e)
       if (P.G[e] == kDeep) { e0 = e; if (!emin) emin = e; }
     if (e0) {
-      const ChainResult r = run_fwd_chain(ix, C32, P, e0, P.kmax + (e0 - emin), steps);
+      const ChainResult r = run_fwd_chain(ix, C32, P, e0, P.kmax + (e0 - emin), steps, seeds);
       for (uint32_t e = emin; e <= e0; ++e) {
         if (P.G[e] != kDeep) continue;
         const uint32_t dt = e0 - e;
@@ -640,7 +661,7 @@ NM_HD void free_cert_thread(const DevIndex &ix, const uint32_t *C32, const SegPa
     }
   }
   // ---- other strand: chain from the SMALLEST deep start i0; it contains seg[i', i'+L) for every larger i'
-  if (P.use_rc) {
+  if (P.use_rc && (parts & 2u)) {
     const uint32_t first = t * gs;
     uint32_t end = first + gs;
     if (end > P.num_kmers) end = P.num_kmers;
@@ -648,7 +669,7 @@ NM_HD void free_cert_thread(const DevIndex &ix, const uint32_t *C32, const SegPa
     for (uint32_t i = first; i < end; ++i)
       if (P.R[i] == kDeep) { if (i0 == kNoBarrier) i0 = i; imax = i; }
     if (i0 != kNoBarrier) {
-      const ChainResult r = run_rc_chain(ix, C32, P, i0, P.kmax + (imax - i0), steps);
+      const ChainResult r = run_rc_chain(ix, C32, P, i0, P.kmax + (imax - i0), steps, seeds);
       for (uint32_t i = i0; i <= imax; ++i) {
         if (P.R[i] != kDeep) continue;
         const uint32_t dt = i - i0;
@@ -824,6 +845,35 @@ NM_HD void seed_transcode_thread(const uint64_t *seed64, SeedEntry32 *seed32, ui
   o.start = (uint32_t)s;
   o.len = (s <= e) ? (uint32_t)(e - s + 1) : 0u;
   seed32[t] = o;
+}
+
+// Deeper seed table, derived on the device at load time (one thread per entry of the level above): the
+// SA interval of the (d+1)-mer c.w is one backward-extension step (AwFmSearch.c:44-95) of the interval of
+// the d-mer w, and its key is c * 4^d + key(w) because the leftmost character is the most significant
+// digit (AwFmKmerTable.c:24-35).  Both rank blocks are loaded once for the four letters.
+NM_HD void seed_extend_thread(const DevIndex &ix, const uint32_t *C32, const SeedEntry32 *src, uint32_t d,
+                              SeedEntry32 *dst, uint64_t key) {
+  const SeedEntry32 s = src[key];
+  const uint64_t stride = 1ull << (2 * d);
+  if (s.len == 0) {
+    for (unsigned c = 0; c < 4u; ++c) dst[c * stride + key] = SeedEntry32{0u, 0u};
+    return;
+  }
+  const uint32_t lo = s.start, hi = s.start + s.len;
+  const Rank32Block a = ld_rank32(ix.rank32, lo >> 6);
+  const Rank32Block b = (hi >> 6) == (lo >> 6) ? a : ld_rank32(ix.rank32, hi >> 6);
+  const bool poison = a.c[0] == kPoison || b.c[0] == kPoison;
+  for (unsigned c = 0; c < 4u; ++c) {
+    uint32_t nlo, nhi;
+    if (!poison) {
+      nlo = occ_in_block(a, c, lo & 63u);
+      nhi = occ_in_block(b, c, hi & 63u);
+    } else {
+      nlo = (uint32_t)occ_native(ix.native, c, lo);
+      nhi = (uint32_t)occ_native(ix.native, c, hi);
+    }
+    dst[c * stride + key] = SeedEntry32{nhi > nlo ? C32[c] + nlo : 0u, nhi > nlo ? nhi - nlo : 0u};
+  }
 }
 
 // FNV-1a-like fold used by nm_workspace_checksum (order independent: sum of per-position hashes)

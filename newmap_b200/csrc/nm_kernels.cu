@@ -35,6 +35,15 @@ __global__ void __launch_bounds__(kBlock) k_seed_transcode(const uint64_t *seed6
   if (t < n) seed_transcode_thread(seed64, seed32, t);
 }
 
+// one level of the deeper seed table: thread = one entry of depth d, writes its four children of depth d + 1
+__global__ void __launch_bounds__(kBlock) k_seed_extend(DevIndex ix, const SeedEntry32 *src, uint32_t d, SeedEntry32 *dst) {
+  __shared__ uint32_t sC[8];
+  if (threadIdx.x < 6) sC[threadIdx.x] = ix.c32[threadIdx.x];
+  __syncthreads();
+  const uint64_t key = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (key < (1ull << (2 * d))) seed_extend_thread(ix, sC, src, d, dst, key);
+}
+
 template <bool RC>
 __global__ void __launch_bounds__(kBlock) k_count(DevIndex ix, const uint8_t *seq, const uint64_t *idx,
                                                   const uint64_t *len, uint64_t n, uint32_t *counts,
@@ -55,7 +64,7 @@ static_assert(kTile == 64 && kPrepV * 8 == (int)kTile, "prep kernel assumes 8 th
 __global__ void __launch_bounds__(kBlock) k_prep(DevIndex ix, SegParams P) {
   const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
   const uint64_t p0 = (uint64_t)t * kPrepV;
-  const uint32_t sl = ix.seed_len;
+  const uint32_t sl = P.sl;
   const bool live = p0 < P.seg_len;
   uint32_t first_barrier = kNoBarrier;
   unsigned long long cw = 0;  // the thread's 8 codes, one per byte (no dynamically indexed arrays: no local memory)
@@ -83,8 +92,9 @@ __global__ void __launch_bounds__(kBlock) k_prep(DevIndex ix, SegParams P) {
 #pragma unroll
     for (int i = 0; i < kPrepV; ++i) {
       push(sl - 1 + i);
-      keys[i] = bad ? kSeedInvalid : key;
-    }
+      keys[i] = bad ? 0u : key;
+      if (bad) cw |= (unsigned long long)kSeedBad << (8 * i);  // after code_at(j < kPrepV) has been consumed: push() only
+    }                                                           // reads the letter / irregular / barrier bits of cw
     if (p0 + kPrepV <= P.seg_len) {
       *reinterpret_cast<uint2 *>(P.codes + p0) = make_uint2((uint32_t)cw, (uint32_t)(cw >> 32));
       uint4 *kd = reinterpret_cast<uint4 *>(P.seedkey + p0);
@@ -149,19 +159,121 @@ __global__ void __launch_bounds__(kBlock, 8) k_free_chain(DevIndex ix, SegParams
   __shared__ uint32_t sC[8];
   const uint32_t *C32 = stage_c32(ix, sC);
   const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
-  uint32_t steps = 0;
-  if (p <= P.seg_len) free_chain_thread(ix, C32, P, p, first, steps);
-  flush_counter(&P.counters[CTR_LF], steps);
+  uint32_t steps = 0, seeds = 0;
+  if (p <= P.seg_len) free_chain_thread(ix, C32, P, p, first, steps, seeds);
+  flush_counter(&P.counters[first ? CTR_LF_PASS1 : CTR_LF], steps);  // nm_lib.cu adds the first pass into lf_steps
+  flush_counter(&P.counters[first ? CTR_SEEDS_PASS1 : CTR_SEEDS], seeds);
 }
 
-// pass 2: one thread per group of P.gsize positions
-__global__ void __launch_bounds__(kBlock, 8) k_free_cert(DevIndex ix, SegParams P, uint32_t ngroups) {
+// pass 1, tiled: one block = kP1Tile consecutive positions = 2 * kP1Tile chains (forward strand ending at p, other
+// strand starting at p).  With a deep seed table most chains are over after their table lookup, so:
+//   phase A  every thread issues its four seed lookups back to back (four independent random sectors in flight per
+//            thread, no divergence), settles the chains that are already decided and queues the rest in shared memory;
+//   phase B  the lanes pop queued chains and extend them one step per iteration, taking the next chain as soon as
+//            theirs ends, so the warps stay full while the DRAM latency of each step is covered by the other lanes.
+// Same values as free_chain_thread(first = true) (nm_core.cuh) position by position.
+constexpr int kP1Tile = 2 * kBlock;
+
+__global__ void __launch_bounds__(kBlock, 8) k_pass1_tiled(DevIndex ix, SegParams P) {
+  __shared__ uint32_t sC[8];
+  __shared__ uint4 s_items[2 * kP1Tile];  // {p, lo, hi, d | kind << 31}
+  __shared__ uint32_t s_count, s_next;
+  if (threadIdx.x == 0) s_count = s_next = 0;
+  const uint32_t *C32 = stage_c32(ix, sC);  // __syncthreads inside
+  const uint32_t cap = P.dcap < P.kmax ? P.dcap : P.kmax;
+  const uint32_t t0 = blockIdx.x * kP1Tile;
+  uint32_t steps = 0, seeds = 0;
+
+  // ---- phase A: the code bytes of all four chains, then their seed keys, then their table entries, each group
+  // issued together so that the loads of one group are in flight at the same time
+  SeedEntry32 ent[4];
+  uint32_t st[4];  // 0 outside the segment, 1 not wanted, 2 starts from a letter, 3 starts from the seed table
+  {
+    uint32_t cprev[2], cself[2], cwin[2];  // codes[p - 1], codes[p], codes[p - sl]
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const uint32_t p = t0 + j * kBlock + threadIdx.x;
+      cprev[j] = (p >= 1u && p <= P.seg_len) ? (uint32_t)ld8(P.codes + p - 1) : (uint32_t)kBarrier;
+      cself[j] = p < P.seg_len ? (uint32_t)ld8(P.codes + p) : (uint32_t)(kNoStart | kSeedBad);
+      cwin[j] = (p >= P.sl && p <= P.seg_len) ? (uint32_t)ld8(P.codes + p - P.sl) : (uint32_t)kSeedBad;
+    }
+    uint32_t key[4];
+#pragma unroll
+    for (int slot = 0; slot < 4; ++slot) {
+      const int j = slot >> 1;
+      const uint32_t p = t0 + j * kBlock + threadIdx.x, kind = slot & 1;
+      uint32_t v = 0;
+      if (kind == 0u) {  // fwd_wanted / chain_seeded(kind 0) on the bytes already loaded
+        if (p <= P.seg_len) v = (p >= 1u && !(cprev[j] & kBarrier)) ? ((!(cwin[j] & kSeedBad) && !(P.mode == 1 && p == P.seg_len)) ? 3u : 2u) : 1u;
+      } else {           // rc_wanted / chain_seeded(kind 1)
+        if (p < P.seg_len) v = (P.use_rc && p < P.num_kmers && !(cself[j] & kNoStart)) ? (!(cself[j] & kSeedBad) ? 3u : 2u) : 1u;
+      }
+      st[slot] = v;
+      key[slot] = v == 3u ? ld32(P.seedkey + (kind == 0u ? p - P.sl : p)) : 0u;
+    }
+#pragma unroll
+    for (int slot = 0; slot < 4; ++slot) {
+      const uint32_t k = (slot & 1) ? rc_seed_key(key[slot], P.sl) : key[slot];
+      ent[slot] = SeedEntry32{0u, 0u};
+      if (st[slot] == 3u) {
+        const uint2 e = __ldg(reinterpret_cast<const uint2 *>(P.seedtab + k));
+        ent[slot] = SeedEntry32{e.x, e.y};
+      }
+    }
+  }
+#pragma unroll
+  for (int slot = 0; slot < 4; ++slot) {
+    const uint32_t p = t0 + (slot >> 1) * kBlock + threadIdx.x, kind = slot & 1;
+    if (st[slot] == 0) continue;
+    uint32_t *dst = kind == 0u ? P.G + p : P.R + p;
+    const uint32_t none = kind == 0u ? kNone : kInf;
+    if (st[slot] == 1) { *dst = none; continue; }
+    if (st[slot] == 3) ++seeds;
+    const ChainState s = st[slot] == 3 ? chain_from_seed(ent[slot], P.sl) : chain_from_letter(C32, P, kind, p);
+    ChainResult r{0, 0, false};
+    if (chain_finished(P, kind, s, r)) {
+      *dst = chain_value(P, r, cap, none);
+    } else {
+      const uint32_t at = atomicAdd(&s_count, 1u);
+      s_items[at] = make_uint4(p, s.lo, s.hi, s.d | (kind << 31));
+    }
+  }
+  __syncthreads();
+
+  // ---- phase B
+  const uint32_t count = s_count;
+  bool have = false;
+  uint32_t p = 0, kind = 0;
+  ChainState s{0, 0, 0};
+  for (;;) {
+    if (!have) {
+      const uint32_t at = atomicAdd(&s_next, 1u);
+      if (at >= count) break;
+      const uint4 it = s_items[at];
+      p = it.x;
+      s = ChainState{it.y, it.z, it.w & 0x7FFFFFFFu};
+      kind = it.w >> 31;
+      have = true;
+    }
+    ChainResult r{0, 0, false};
+    if (chain_iterate(ix, C32, P, kind, p, s, cap, steps, r)) {
+      *(kind == 0u ? P.G + p : P.R + p) = chain_value(P, r, cap, kind == 0u ? kNone : kInf);
+      have = false;
+    }
+  }
+  flush_counter(&P.counters[CTR_LF_PASS1], steps);
+  flush_counter(&P.counters[CTR_SEEDS_PASS1], seeds);
+}
+
+// pass 2: two threads per group of P.gsize positions (forward-strand chain, other-strand chain)
+__global__ void __launch_bounds__(64, 16) k_free_cert(DevIndex ix, SegParams P, uint32_t ngroups) {
   __shared__ uint32_t sC[8];
   const uint32_t *C32 = stage_c32(ix, sC);
   const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-  uint32_t steps = 0;
-  if (t < ngroups) free_cert_thread(ix, C32, P, t, steps);
+  uint32_t steps = 0, seeds = 0;
+  if ((t >> 1) < ngroups) free_cert_thread(ix, C32, P, t >> 1, steps, seeds, 1u << (t & 1u));
   flush_counter(&P.counters[CTR_LF], steps);
+  flush_counter(&P.counters[CTR_SEEDS], seeds);
 }
 
 __global__ void __launch_bounds__(kBlock) k_free_generic(DevIndex ix, SegParams P, bool all) {
@@ -237,6 +349,9 @@ void launch_transcode(const uint8_t *native, uint64_t n_blocks, uint64_t bwt_len
 void launch_seed_transcode(const uint64_t *seed64, SeedEntry32 *seed32, uint64_t entries, cudaStream_t st) {
   k_seed_transcode<<<grid_for(entries), kBlock, 0, st>>>(seed64, seed32, entries);
 }
+void launch_seed_extend(const DevIndex &ix, const SeedEntry32 *src, uint32_t d, SeedEntry32 *dst, cudaStream_t st) {
+  k_seed_extend<<<grid_for(1ull << (2 * d)), kBlock, 0, st>>>(ix, src, d, dst);
+}
 void launch_count(const DevIndex &ix, const uint8_t *seq, const uint64_t *idx, const uint64_t *len, uint64_t n,
                   bool rc, uint32_t *counts, unsigned long long *counters, cudaStream_t st) {
   if (n == 0) return;
@@ -251,14 +366,15 @@ void launch_trajectory(const DevIndex &ix, const SegParams &P, cudaStream_t st) 
   if (P.num_kmers == 0) return;
   k_trajectory<<<grid_for(P.num_kmers), kBlock, 0, st>>>(ix, P);
 }
-void launch_free_fast(const DevIndex &ix, const SegParams &P, cudaStream_t st) {
-  const uint64_t n = (uint64_t)P.seg_len + 1;
-  k_free_chain<<<grid_for(n), kBlock, 0, st>>>(ix, P, true);
-  if (P.dcap < P.kmax) {
-    const uint32_t ngroups = (uint32_t)((n + P.gsize - 1) / P.gsize);
-    k_free_cert<<<grid_for(ngroups, 64), 64, 0, st>>>(ix, P, ngroups);
-    k_free_chain<<<grid_for(n), kBlock, 0, st>>>(ix, P, false);
-  }
+void launch_free_chain(const DevIndex &ix, const SegParams &P, bool first, cudaStream_t st) {
+  k_free_chain<<<grid_for((uint64_t)P.seg_len + 1), kBlock, 0, st>>>(ix, P, first);
+}
+void launch_free_pass1(const DevIndex &ix, const SegParams &P, cudaStream_t st) {
+  k_pass1_tiled<<<grid_for((uint64_t)P.seg_len + 1, kP1Tile), kBlock, 0, st>>>(ix, P);
+}
+void launch_free_cert(const DevIndex &ix, const SegParams &P, cudaStream_t st) {
+  const uint32_t ngroups = (uint32_t)(((uint64_t)P.seg_len + 1 + P.gsize - 1) / P.gsize);
+  k_free_cert<<<grid_for(2ull * ngroups, 64), 64, 0, st>>>(ix, P, ngroups);
 }
 void launch_free_generic(const DevIndex &ix, const SegParams &P, bool all, cudaStream_t st) {
   k_free_generic<<<grid_for((uint64_t)P.seg_len + 1), kBlock, 0, st>>>(ix, P, all);

@@ -9,11 +9,14 @@ namespace nm {
 void launch_transcode(const uint8_t *native, uint64_t n_blocks, uint64_t bwt_len, uint32_t *rank32,
                       uint64_t n64_total, cudaStream_t st);
 void launch_seed_transcode(const uint64_t *seed64, SeedEntry32 *seed32, uint64_t entries, cudaStream_t st);
+void launch_seed_extend(const DevIndex &ix, const SeedEntry32 *src, uint32_t d, SeedEntry32 *dst, cudaStream_t st);
 void launch_count(const DevIndex &ix, const uint8_t *seq, const uint64_t *idx, const uint64_t *len, uint64_t n,
                   bool rc, uint32_t *counts, unsigned long long *counters, cudaStream_t st);
 void launch_prep(const DevIndex &ix, const SegParams &P, cudaStream_t st);
 void launch_trajectory(const DevIndex &ix, const SegParams &P, cudaStream_t st);
-void launch_free_fast(const DevIndex &ix, const SegParams &P, cudaStream_t st);
+void launch_free_chain(const DevIndex &ix, const SegParams &P, bool first, cudaStream_t st);  // pass 1 / pass 3
+void launch_free_pass1(const DevIndex &ix, const SegParams &P, cudaStream_t st);                 // pass 1, tiled kernel
+void launch_free_cert(const DevIndex &ix, const SegParams &P, cudaStream_t st);               // pass 2
 void launch_free_generic(const DevIndex &ix, const SegParams &P, bool all, cudaStream_t st);
 void launch_resolve(const DevIndex &ix, const SegParams &P, cudaStream_t st);
 void launch_checksum(const void *out, int out_width, uint64_t n, unsigned long long *sum, cudaStream_t st);

@@ -28,6 +28,7 @@ int cuda_fail(cudaError_t e, const char *what) {
     if (e__ != cudaSuccess) return cuda_fail(e__, #call); \
   } while (0)
 
+
 }  // namespace
 
 struct nm_index {
@@ -39,6 +40,8 @@ struct nm_index {
   bool has_rank32 = false;
   uint64_t device_bytes = 0;
   void *d_native = nullptr, *d_rank32 = nullptr, *d_seed32 = nullptr, *d_seed64 = nullptr, *d_c32 = nullptr;
+  void *d_seedx = nullptr;             // deeper seed table derived on the device (set_seed_depth)
+  uint64_t seedx_bytes = 0;
   nm_workspace *default_ws = nullptr;  // used by nm_min_unique
   std::mutex mu;                       // serialises calls that share default_ws / count scratch
 };
@@ -56,7 +59,8 @@ struct nm_workspace {
   uint32_t klist_cap = 0;
   unsigned long long *d_counters = nullptr;
   unsigned long long *h_counters = nullptr;  // pinned
-  cudaEvent_t ev[8]{};
+  cudaEvent_t ev[10]{};
+  uint32_t launches = 0;  // kernels launched by the last search (run_search)
   // last call
   nm::SegParams P{};
   uint64_t seg_len = 0;
@@ -64,7 +68,7 @@ struct nm_workspace {
   int algo_req = 0, algo_used = 0;
   bool timed_h2d = false, timed_d2h = false;
   void *pending_out = nullptr;
-  uint32_t opt_ref_lf = 0, opt_dcap = 0, opt_gsize = 0;
+  uint32_t opt_ref_lf = 0, opt_dcap = 0, opt_gsize = 0, opt_pass1 = 0;
 };
 
 namespace {
@@ -73,6 +77,62 @@ namespace {
 // u8 suffixArrayCompressionRatio | u8 kmerLengthInSeedTable | u8 alphabetType | u8 storeOriginalSequence |
 // u64 bwtLength | blocks | u64 prefixSums[6] | seed table | ...
 constexpr size_t kHeaderBytes = 30;
+
+// Deeper seed table: level d+1 from level d with one backward-extension step per entry, starting from the
+// index's own table.  depth 0 (or <= seed_len) drops it.  Needs the rank32 layout.
+int set_seed_depth(nm_index *ix, uint32_t depth) {
+  NM_CUDA(cudaSetDevice(ix->device));
+  NM_CUDA(cudaDeviceSynchronize());
+  if (ix->d_seedx) {
+    cudaFree(ix->d_seedx);
+    ix->d_seedx = nullptr;
+    ix->device_bytes -= ix->seedx_bytes;
+    ix->seedx_bytes = 0;
+    ix->dev.seedx = nullptr;
+    ix->dev.seedx_len = 0;
+  }
+  const uint32_t sl = ix->dev.seed_len;
+  if (depth <= sl) return NM_OK;
+  if (!ix->has_rank32 || depth > 16) return NM_EUNSUPPORTED;
+  void *cur = ix->d_seed32;
+  for (uint32_t d = sl; d < depth; ++d) {
+    void *next = nullptr;
+    const size_t bytes = (size_t)sizeof(nm::SeedEntry32) << (2 * (d + 1));
+    if (cudaMalloc(&next, bytes) != cudaSuccess) {
+      cudaGetLastError();
+      if (cur != ix->d_seed32) cudaFree(cur);
+      return NM_EALLOC;
+    }
+    nm::launch_seed_extend(ix->dev, (const nm::SeedEntry32 *)cur, d, (nm::SeedEntry32 *)next, 0);
+    const cudaError_t e = cudaDeviceSynchronize();
+    if (cur != ix->d_seed32) cudaFree(cur);
+    cur = next;
+    if (e != cudaSuccess) {
+      cudaFree(cur);
+      return cuda_fail(e, "k_seed_extend");
+    }
+  }
+  ix->d_seedx = cur;
+  ix->seedx_bytes = (uint64_t)sizeof(nm::SeedEntry32) << (2 * depth);
+  ix->device_bytes += ix->seedx_bytes;
+  ix->dev.seedx = (const nm::SeedEntry32 *)cur;
+  ix->dev.seedx_len = depth;
+  return NM_OK;
+}
+
+// Depth chosen at load time: the smallest d with 4^d >= 4 * bwtLength (beyond that almost every d-mer of the
+// text is already unique, so a chain is one table lookup plus a step or two), at most 16 (u32 keys), and the
+// table plus its parent level within a third of the free device memory.  NEWMAP_B200_SEED_DEPTH overrides
+// (0 = none).  Purely a speed matter: results do not depend on it.
+uint32_t auto_seed_depth(const nm_index *ix) {
+  if (const char *v = getenv("NEWMAP_B200_SEED_DEPTH")) return (uint32_t)strtoul(v, nullptr, 10);
+  uint32_t d = ix->dev.seed_len;
+  while (d < 16 && (1ull << (2 * d)) < 4 * ix->dev.bwt_len) ++d;
+  size_t free_b = 0, total_b = 0;
+  if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) return 0;
+  while (d > ix->dev.seed_len && ((10ull << (2 * d)) > free_b / 3)) --d;  // 8 B x 4^d + 8 B x 4^(d-1)
+  return d;
+}
 
 int load_index(const char *path, int device, nm_index **out) {
   int ndev = 0;
@@ -176,6 +236,8 @@ int load_index(const char *path, int device, nm_index **out) {
     ix->dev.rank32 = (const uint32_t *)ix->d_rank32;
     ix->dev.seed32 = (const nm::SeedEntry32 *)ix->d_seed32;
     ix->has_rank32 = true;
+    const int rc = set_seed_depth(ix, auto_seed_depth(ix));
+    if (rc != NM_OK && rc != NM_EALLOC && rc != NM_EUNSUPPORTED) return rc;  // without the table the searches still run
   }
   guard.ix = nullptr;
   *out = ix;
@@ -199,7 +261,7 @@ int ws_alloc(nm_workspace *ws) {
   return NM_OK;
 }
 
-enum { EV_H2D0 = 0, EV_H2D1, EV_PREP1, EV_SEARCH1, EV_GENERIC1, EV_RESOLVE1, EV_D2H0, EV_D2H1 };
+enum { EV_H2D0 = 0, EV_H2D1, EV_PREP1, EV_PASS1, EV_CERT1, EV_SEARCH1, EV_GENERIC1, EV_RESOLVE1, EV_D2H0, EV_D2H1 };
 
 // launches prep + the chosen algorithm on ws->stream; nothing is synchronised here
 int run_search(nm_workspace *ws, int algo) {
@@ -210,20 +272,37 @@ int run_search(nm_workspace *ws, int algo) {
   NM_CUDA(cudaMemcpyAsync(ws->d_counters, init_counters, sizeof init_counters, cudaMemcpyHostToDevice, st));
   NM_CUDA(cudaEventRecord(ws->ev[EV_H2D1], st));
   nm::launch_prep(ix->dev, P, st);
+  ws->launches = P.seg_len ? 1u : 0u;
   NM_CUDA(cudaEventRecord(ws->ev[EV_PREP1], st));
   if (algo == NM_ALGO_TRAJECTORY) {
     nm::launch_trajectory(ix->dev, P, st);
+    ws->launches += P.num_kmers ? 1u : 0u;
+    NM_CUDA(cudaEventRecord(ws->ev[EV_PASS1], st));
+    NM_CUDA(cudaEventRecord(ws->ev[EV_CERT1], st));
     NM_CUDA(cudaEventRecord(ws->ev[EV_SEARCH1], st));
     NM_CUDA(cudaEventRecord(ws->ev[EV_GENERIC1], st));
     NM_CUDA(cudaEventRecord(ws->ev[EV_RESOLVE1], st));
   } else {
     const bool fast = (algo != NM_ALGO_FREE_GENERIC) && ix->has_rank32 && P.kmin >= ix->dev.seed_len;
     P.fast = fast ? 1 : 0;
-    if (fast) nm::launch_free_fast(ix->dev, P, st);
+    const bool deep_passes = fast && P.dcap < P.kmax;
+    if (fast) {
+      // tiled kernel when the chains are short (deep seed table); with the file's 12-letter table the chains run
+      // 4-5 steps on average and one thread per position is faster (measured: profiles/r1_seed_depth_sweep.md)
+      const bool tiled = ws->opt_pass1 == 2u || (ws->opt_pass1 == 0u && P.sl >= 13u);
+      if (tiled) nm::launch_free_pass1(ix->dev, P, st);
+      else nm::launch_free_chain(ix->dev, P, true, st);
+      ++ws->launches;
+    }
+    NM_CUDA(cudaEventRecord(ws->ev[EV_PASS1], st));
+    if (deep_passes) { nm::launch_free_cert(ix->dev, P, st); ++ws->launches; }
+    NM_CUDA(cudaEventRecord(ws->ev[EV_CERT1], st));
+    if (deep_passes) { nm::launch_free_chain(ix->dev, P, false, st); ++ws->launches; }
     NM_CUDA(cudaEventRecord(ws->ev[EV_SEARCH1], st));
-    if (!fast) nm::launch_free_generic(ix->dev, P, true, st);
+    if (!fast) { nm::launch_free_generic(ix->dev, P, true, st); ++ws->launches; }
     NM_CUDA(cudaEventRecord(ws->ev[EV_GENERIC1], st));
     nm::launch_resolve(ix->dev, P, st);
+    ws->launches += P.num_kmers ? 1u : 0u;
     NM_CUDA(cudaEventRecord(ws->ev[EV_RESOLVE1], st));
   }
   NM_CUDA(cudaGetLastError());
@@ -275,9 +354,16 @@ void nm_index_close(nm_index *ix) {
   cudaFree(ix->d_native);
   cudaFree(ix->d_rank32);
   cudaFree(ix->d_seed32);
+  cudaFree(ix->d_seedx);
   cudaFree(ix->d_seed64);
   cudaFree(ix->d_c32);
   delete ix;
+}
+
+int nm_index_set_seed_depth(nm_index *ix, uint32_t depth) {
+  if (!ix) return NM_EARG;
+  std::lock_guard<std::mutex> lock(ix->mu);
+  return set_seed_depth(ix, depth);
 }
 
 int nm_index_info_get(const nm_index *ix, nm_index_info *info) {
@@ -287,6 +373,7 @@ int nm_index_info_get(const nm_index *ix, nm_index_info *info) {
   for (int l = 0; l < 6; ++l) info->prefix_sums[l] = ix->dev.C[l];
   info->device_bytes = ix->device_bytes;
   info->seed_length = ix->dev.seed_len;
+  info->derived_seed_length = ix->dev.seedx_len;
   info->sa_compression_ratio = ix->sa_ratio;
   info->has_rank32 = ix->has_rank32 ? 1u : 0u;
   info->device = ix->device;
@@ -454,10 +541,16 @@ int nm_workspace_search(nm_workspace *ws, uint64_t num_kmers, int mode, const ui
   P.use_rc = use_rc ? 1 : 0;
   P.out_width = out_width;
   P.fast = 0;
-  P.want_ref_lf = ws->opt_ref_lf ? 1 : 0;
   {
-    const uint32_t sl = ws->ix->dev.seed_len;
-    P.dcap = ws->opt_dcap ? ws->opt_dcap : sl + 12;
+    // chains start from the deeper derived table when every queried length reaches its depth; the estimate of the
+    // reference's LF steps (NM_OPT_REF_LF) needs thresholds exact down to the index's own seed length
+    const nm::DevIndex &dv = ws->ix->dev;
+    const bool deep = dv.seedx && kmin >= dv.seedx_len && ws->opt_ref_lf != 2u;
+    P.want_ref_lf = (ws->opt_ref_lf && !deep) ? 1 : 0;
+    P.sl = deep ? dv.seedx_len : dv.seed_len;
+    P.seedtab = deep ? dv.seedx : dv.seed32;
+    const uint32_t sl = P.sl;
+    P.dcap = ws->opt_dcap ? ws->opt_dcap : (deep ? sl + 8 : sl + 12);
     if (P.dcap <= sl) P.dcap = sl + 1;
     P.gsize = ws->opt_gsize ? ws->opt_gsize : 32;
   }
@@ -487,16 +580,23 @@ int nm_workspace_sync(nm_workspace *ws, nm_stats *stats) {
   NM_CUDA(cudaStreamSynchronize(ws->stream));
   if (!ws->have_search) return NM_OK;
   bool replayed = false;
-  float ms[7] = {0, 0, 0, 0, 0, 0, 0};
+  float ms[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
   auto el = [&](int a, int b, float &dst) { cudaEventElapsedTime(&dst, ws->ev[a], ws->ev[b]); };
   if (ws->timed_h2d) el(EV_H2D0, EV_H2D1, ms[0]);
   el(EV_H2D1, EV_PREP1, ms[1]);
   el(EV_PREP1, EV_SEARCH1, ms[2]);
+  el(EV_PREP1, EV_PASS1, ms[7]);
+  el(EV_PASS1, EV_CERT1, ms[8]);
+  el(EV_CERT1, EV_SEARCH1, ms[9]);
   el(EV_SEARCH1, EV_GENERIC1, ms[3]);
   el(EV_GENERIC1, EV_RESOLVE1, ms[4]);
   if (ws->timed_d2h) el(EV_D2H0, EV_D2H1, ms[5]);
   if (ws->timed_d2h) el(EV_H2D0, EV_D2H1, ms[6]); else el(EV_H2D0, EV_RESOLVE1, ms[6]);
-  unsigned long long free_lf = ws->h_counters[nm::CTR_LF];
+  const uint32_t free_launches = ws->launches;
+  const unsigned long long lf_pass1 = ws->h_counters[nm::CTR_LF_PASS1],
+                           seeds_pass1 = ws->h_counters[nm::CTR_SEEDS_PASS1],
+                           seeds = ws->h_counters[nm::CTR_SEEDS] + seeds_pass1;
+  unsigned long long free_lf = ws->h_counters[nm::CTR_LF] + lf_pass1;
   if (ws->algo_req == NM_ALGO_AUTO && ws->h_counters[nm::CTR_ANOMALY]) {
     // A substring of the segment is absent from the index (sequence / index mismatch).  The
     // reference reports the first zero count on ITS query trajectory: replay that trajectory.
@@ -514,7 +614,15 @@ int nm_workspace_sync(nm_workspace *ws, nm_stats *stats) {
   if (stats) {
     memset(stats, 0, sizeof *stats);
     stats->positions = ws->P.num_kmers;
-    stats->lf_steps = ws->h_counters[nm::CTR_LF] + (replayed ? free_lf : 0);
+    stats->lf_steps = ws->h_counters[nm::CTR_LF] + (replayed ? free_lf : lf_pass1);
+    stats->lf_steps_pass1 = lf_pass1;
+    stats->seed_lookups = seeds;
+    stats->seed_lookups_pass1 = seeds_pass1;
+    stats->launches = ws->launches + (replayed ? free_launches : 0u);
+    stats->seed_depth = ws->P.sl;
+    stats->ms_pass1 = ms[7];
+    stats->ms_cert = ms[8];
+    stats->ms_pass3 = ms[9];
     stats->queries = ws->h_counters[nm::CTR_QUERIES];
     stats->generic_searches = ws->h_counters[nm::CTR_GENERIC];
     stats->ref_lf_steps = ws->h_counters[nm::CTR_REF_LF];
@@ -545,8 +653,9 @@ int nm_workspace_sync(nm_workspace *ws, nm_stats *stats) {
 int nm_workspace_option(nm_workspace *ws, int option, uint64_t value) {
   if (!ws) return NM_EARG;
   switch (option) {
-    case NM_OPT_REF_LF: ws->opt_ref_lf = value ? 1u : 0u; return NM_OK;
+    case NM_OPT_REF_LF: ws->opt_ref_lf = value ? 2u : 0u; return NM_OK;  // 2 = asked for explicitly
     case NM_OPT_DCAP: ws->opt_dcap = (uint32_t)value; return NM_OK;
+    case NM_OPT_PASS1: if (value > 2) return NM_EARG; ws->opt_pass1 = (uint32_t)value; return NM_OK;
     case NM_OPT_GSIZE: if (value > 4096) return NM_EARG; ws->opt_gsize = (uint32_t)value; return NM_OK;
     default: return NM_EARG;
   }
@@ -586,7 +695,7 @@ int nm_min_unique(nm_index *ix, const uint8_t *seg, uint64_t seg_len, uint64_t n
     if (rc != NM_OK) return rc;
   }
   nm_workspace *ws = ix->default_ws;
-  ws->opt_ref_lf = stats ? 1u : 0u;
+  ws->opt_ref_lf = stats ? 1u : 0u;  // 1 = computed when the search runs on the index's own seed table anyway
   int rc = nm_workspace_upload(ws, seg, seg_len);
   if (rc == NM_OK) rc = nm_workspace_search(ws, num_kmers, mode, klist, nk, initial_search_length, use_rc, algo, out_width);
   if (rc == NM_OK) rc = nm_workspace_download(ws, out);

@@ -27,6 +27,7 @@ def lib():
         L.emu_index_open.restype = C.c_void_p
         L.emu_index_open.argtypes = [C.c_char_p]
         L.emu_index_close.argtypes = [C.c_void_p]
+        L.emu_index_set_seed_depth.argtypes = [C.c_void_p, C.c_uint32]
         L.emu_count.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_uint64, C.c_int,
                                 C.c_void_p, C.c_void_p]
         L.emu_min_unique.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_int, C.c_void_p, C.c_uint32,
@@ -40,6 +41,11 @@ class EmuIndex:
         self._h = lib().emu_index_open(os.fsencode(str(path)))
         if not self._h:
             raise OSError(f"hostemu: cannot load {path}")
+
+    def set_seed_depth(self, depth: int):
+        if lib().emu_index_set_seed_depth(self._h, depth):
+            raise ValueError(f"hostemu: seed depth {depth} unsupported")
+        return self
 
     def count(self, seq: bytes, idx, length, rc=False):
         idx = np.ascontiguousarray(idx, dtype=np.uint64)

@@ -17,6 +17,7 @@ struct EmuIndex {
   std::vector<uint32_t> rank32;
   std::vector<SeedEntry32> seed32;
   std::vector<uint64_t> seed64;
+  std::vector<SeedEntry32> seedx;  // deeper derived table (emu_index_set_seed_depth)
   uint32_t c32[8] = {0};
   DevIndex dev{};
   bool has_rank32 = false;
@@ -65,6 +66,28 @@ EmuIndex *emu_index_open(const char *path) {
 
 void emu_index_close(EmuIndex *ix) { delete ix; }
 
+uint32_t emu_rc_seed_key(uint32_t key, uint32_t sl) { return rc_seed_key(key, sl); }
+
+// the level-by-level construction nm_lib.cu set_seed_depth runs on the device
+int emu_index_set_seed_depth(EmuIndex *ix, uint32_t depth) {
+  ix->seedx.clear();
+  ix->dev.seedx = nullptr;
+  ix->dev.seedx_len = 0;
+  const uint32_t sl = ix->dev.seed_len;
+  if (depth <= sl) return 0;
+  if (depth > 16) return -8;
+  std::vector<SeedEntry32> cur = ix->seed32;
+  for (uint32_t d = sl; d < depth; ++d) {
+    std::vector<SeedEntry32> next((size_t)1 << (2 * (d + 1)));
+    for (uint64_t key = 0; key < (1ull << (2 * d)); ++key) seed_extend_thread(ix->dev, ix->c32, cur.data(), d, next.data(), key);
+    cur.swap(next);
+  }
+  ix->seedx.swap(cur);
+  ix->dev.seedx = ix->seedx.data();
+  ix->dev.seedx_len = depth;
+  return 0;
+}
+
 int emu_count(EmuIndex *ix, const uint8_t *seq, uint64_t seq_len, const uint64_t *idx, const uint64_t *len,
               uint64_t n, int rc, uint32_t *counts, uint64_t *lf) {
   uint32_t steps = 0;
@@ -87,15 +110,21 @@ int emu_min_unique(EmuIndex *ix, const uint8_t *seg, uint32_t seg_len, uint32_t 
   P.seg = seg; P.codes = codes.data(); P.seedkey = seedkey.data(); P.nb = nb.data(); P.tile_first = tf.data();
   P.G = G.data(); P.R = R.data(); P.out = out; P.klist = klist; P.counters = ctr;
   P.seg_len = seg_len; P.num_kmers = num_kmers; P.nk = nk; P.initial = initial; P.mode = mode;
-  P.use_rc = use_rc; P.out_width = out_width; P.want_ref_lf = 1;
-  P.dcap = dcap ? dcap : ix->dev.seed_len + 12; if (P.dcap <= ix->dev.seed_len) P.dcap = ix->dev.seed_len + 1;
+  P.use_rc = use_rc; P.out_width = out_width;
   P.gsize = gsize ? gsize : 32;
   if (mode == 0) { P.kmin = klist[0]; P.kmax = klist[1]; }
   else { P.kmin = P.kmax = klist[0]; for (uint32_t j = 0; j < nk; ++j) { if (klist[j] < P.kmin) P.kmin = klist[j]; if (klist[j] > P.kmax) P.kmax = klist[j]; } }
+  // nm_lib.cu nm_workspace_search: the deeper table when every queried length reaches its depth (the estimate of the
+  // reference's LF steps is then off, so it is only requested on the index's own table)
+  const bool deep = ix->dev.seedx && P.kmin >= ix->dev.seedx_len;
+  P.sl = deep ? ix->dev.seedx_len : ix->dev.seed_len;
+  P.seedtab = deep ? ix->dev.seedx : ix->dev.seed32;
+  P.want_ref_lf = deep ? 0 : 1;
+  P.dcap = dcap ? dcap : P.sl + 12; if (P.dcap <= P.sl) P.dcap = P.sl + 1;
   for (uint32_t p = 0; p < seg_len; ++p) prep_thread(ix->dev, P, p);
   const uint32_t ntiles = (seg_len + kTile - 1) / kTile;
   for (uint32_t t = 0; t < ntiles; ++t) nb_tile_thread(P, t);
-  uint32_t steps = 0, nq = 0, ns = 0;
+  uint32_t steps = 0, nq = 0, ns = 0, seeds = 0;
   uint64_t ref_lf = 0;
   if (algo == 1) {
     for (uint32_t i = 0; i < num_kmers; ++i) trajectory_thread(ix->dev, P, i, steps, nq);
@@ -103,14 +132,14 @@ int emu_min_unique(EmuIndex *ix, const uint8_t *seg, uint32_t seg_len, uint32_t 
     const bool fast = (algo != 2) && ix->has_rank32 && P.kmin >= ix->dev.seed_len;
     P.fast = fast;
     if (fast) {
-      for (uint32_t p = 0; p <= seg_len; ++p) free_chain_thread(ix->dev, ix->c32, P, p, true, steps);
+      for (uint32_t p = 0; p <= seg_len; ++p) free_chain_thread(ix->dev, ix->c32, P, p, true, steps, seeds);
       if (P.dcap < P.kmax) {
         const uint32_t ngroups = (seg_len + 1 + P.gsize - 1) / P.gsize;
         uint32_t s2 = 0;
-        for (uint32_t t = 0; t < ngroups; ++t) free_cert_thread(ix->dev, ix->c32, P, t, s2);
+        for (uint32_t t = 0; t < ngroups; ++t) free_cert_thread(ix->dev, ix->c32, P, t, s2, seeds);
         ns = s2;  // reported in stats[2]: LF steps of the certificate pass
         steps += s2;
-        for (uint32_t p = 0; p <= seg_len; ++p) free_chain_thread(ix->dev, ix->c32, P, p, false, steps);
+        for (uint32_t p = 0; p <= seg_len; ++p) free_chain_thread(ix->dev, ix->c32, P, p, false, steps, seeds);
       }
     } else {
       for (uint32_t p = 0; p <= seg_len; ++p) free_generic_thread(ix->dev, P, p, true, steps, ns);

@@ -96,6 +96,39 @@ def test_golden_searches(indexes, manifest, golden_searches, algo):
             assert bad.size == 0, (algo, run["id"], sid, bad[:10], arr[bad[:10]], want[bad[:10]])
 
 
+@pytest.mark.parametrize("extra", [0, 1, 3, 6])
+def test_golden_searches_with_derived_seed_table(nm, manifest, golden_searches, extra):
+    """nm_index_set_seed_depth: chains start from a deeper seed table derived on the device; same bytes."""
+    cache, used = {}, 0
+    try:
+        for run in manifest["searches"]:
+            seed = manifest["indexes"][run["index"]]["seed_length"]
+            if run["index"] not in cache:
+                cache[run["index"]] = ix = nm.Index(GOLD / f"{run['index']}.awfmi", device=0)
+                ix.set_seed_depth(seed + extra if extra else 0)
+                assert ix.derived_seed_length == (seed + extra if extra else 0)
+            ix = cache[run["index"]]
+            klist = run_klist(run)
+            max_k = max(klist)
+            used += bool(extra) and min(klist) >= seed + extra
+            got = {}
+            for seg in ora.segments(GOLD / run["fasta"], run["batch"], max_k - 1):
+                n = len(seg.data) if seg.epilogue else len(seg.data) - (max_k - 1)
+                out, st = ix.min_unique(seg.data, n, klist, run["range"], run.get("initial", 0),
+                                        not run.get("norc", False), "auto")
+                assert st.zero_pos == -1 and st.replayed == 0
+                got.setdefault(seg.id, []).append(out)
+            for sid, parts in got.items():
+                want = golden_searches[f"run{run['id']}|{sid.decode()}"]
+                arr = np.concatenate(parts)
+                bad = np.nonzero(arr != want)[0]
+                assert bad.size == 0, (extra, run["id"], sid, bad[:10], arr[bad[:10]], want[bad[:10]])
+        assert used >= 10 or not extra
+    finally:
+        for ix in cache.values():
+            ix.close()
+
+
 def test_reference_unique_goldens(indexes):
     chr1 = [0, 10, 9, 8, 7, 6, 5, 4, 4, 4, 6, 5, 4, 4, 4, 0, 0, 0, 0, 0]      # reference tests/test_unique_counts.py:17-21
     chr2 = [10, 10, 9, 8, 7, 6, 5, 4, 4, 4] + [0] * 20
@@ -131,7 +164,12 @@ def test_stats_match_oracle_trajectory(indexes):
     assert b"N" not in clean[:2300 + 199 - 1] or True
     o2 = ora.OracleIndex(GOLD / "quirk_s4.awfmi")
     o2.min_unique_segment(seq[:2300 + 39], 2300, list(range(8, 41)), True, nthreads=1)
-    _, st3 = ix.min_unique(seq[:2300 + 39], 2300, list(range(8, 41)), True, algo="auto", dtype=np.uint32)
+    depth = ix.derived_seed_length
+    ix.set_seed_depth(0)         # the estimate needs thresholds exact down to the file's seed length
+    try:
+        _, st3 = ix.min_unique(seq[:2300 + 39], 2300, list(range(8, 41)), True, algo="auto", dtype=np.uint32)
+    finally:
+        ix.set_seed_depth(depth)
     assert st3.ref_lf_steps == o2.lf_steps
 
 
@@ -217,7 +255,15 @@ def test_large_segment_properties_and_cross_algorithm_checksum(nm, tmp_path):
         a, st_a = ix.min_unique(seg, 10_000_000, kl, True, algo="auto")
         b, st_b = ix.min_unique(seg, 10_000_000, kl, True, algo="trajectory")
         assert np.array_equal(a, b)
-        assert st_a.ref_lf_steps > 0 and st_a.lf_steps < st_b.lf_steps
+        assert st_a.lf_steps < st_b.lf_steps
+        assert ix.derived_seed_length > ix.seed_length       # 12 M bases: nm_index_open derives a deeper table
+        ix.set_seed_depth(0)
+        a0, st_a0 = ix.min_unique(seg, 10_000_000, kl, True, algo="auto")
+        assert np.array_equal(a0, a) and st_a0.ref_lf_steps > 0 and st_a.lf_steps < st_a0.lf_steps
+        ix.set_seed_depth(16)
+        assert ix.derived_seed_length == 16
+        a16, st_a16 = ix.min_unique(seg, 10_000_000, kl, True, algo="auto")
+        assert np.array_equal(a16, a) and st_a16.lf_steps <= st_a.lf_steps
         arr = np.frombuffer(seg, dtype=np.uint8)[:10_000_000]
         assert not a[arr == ord("N")].any()
         rng = np.random.default_rng(0)
@@ -252,13 +298,15 @@ def test_tuning_options_do_not_change_results(nm, indexes):
     buf.array[:] = np.frombuffer(seq, dtype=np.uint8)
     out = nm.PinnedBuffer(len(seq))
     ws = nm.Workspace(ix, len(seq))
-    for dcap, gsize in ((0, 0), (7, 1), (8, 5), (13, 64), (40, 200), (1000, 32)):
+    for dcap, gsize, pass1 in ((0, 0, 0), (0, 0, 1), (0, 0, 2), (7, 1, 2), (8, 5, 1), (13, 64, 2), (40, 200, 2), (40, 200, 1),
+                               (1000, 32, 2)):
         ws.option("dcap", dcap)
         ws.option("gsize", gsize)
+        ws.option("pass1", pass1)     # first-pass kernel: tiled with lane refill / one thread per position
         ws.upload(buf.ptr, len(seq))
         ws.search(len(seq), kl, True, out_width=1)
         ws.download(out.ptr)
         st = ws.sync()
         assert st.replayed == 0
-        assert np.array_equal(out.array[:len(seq)], want), (dcap, gsize)
+        assert np.array_equal(out.array[:len(seq)], want), (dcap, gsize, pass1)
     ws.close()

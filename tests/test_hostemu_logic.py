@@ -107,6 +107,7 @@ def test_random_small_genomes_all_algorithms_agree_with_oracle(tmp_path):
         ixp = tmp_path / f"t{trial}.awfmi"
         ora.ref_build_index(fa, ixp, 8, seed)
         o, e = ora.OracleIndex(ixp), EmuIndex(ixp)
+        deep = EmuIndex(ixp).set_seed_depth(seed + 1 + trial % 3)
         for klist, is_range in ((list(range(3, 40)), True), (list(range(seed, 70)), True), ([5, 9, 17, 40], False),
                                 ([30, 12, 12, 50], False)):
             batch = int(rng.integers(20, 500))
@@ -117,6 +118,8 @@ def test_random_small_genomes_all_algorithms_agree_with_oracle(tmp_path):
                 for algo in (0, 1, 2):
                     got, st = e.min_unique_segment(seg.data, n, klist, is_range, algo=algo)
                     assert np.array_equal(got, want), (trial, klist[:3], is_range, algo, batch)
+                got, st = deep.min_unique_segment(seg.data, n, klist, is_range, algo=0)
+                assert np.array_equal(got, want), (trial, klist[:3], is_range, "derived seed table", batch)
 
 
 @pytest.mark.parametrize("dcap_extra,gsize", [(1, 1), (1, 5), (2, 32), (4, 64), (12, 32), (3, 200), (1000, 32)])
@@ -139,3 +142,62 @@ def test_certificate_pass_is_exact_for_any_cap_and_group(manifest, golden_search
             arr = np.concatenate(parts)
             bad = np.nonzero(arr != want)[0]
             assert bad.size == 0, (dcap_extra, gsize, run, sid, bad[:10], arr[bad[:10]], want[bad[:10]])
+
+
+@pytest.mark.parametrize("extra", [1, 2, 4, 6])
+def test_derived_seed_table_never_changes_a_result(manifest, golden_searches, extra):
+    """The deeper seed table derived at load time (nm_index_set_seed_depth) is a speed matter only: every golden
+    search whose shortest length reaches the derived depth starts its chains from it and returns the same bytes."""
+    cache, used = {}, 0
+    for run in manifest["searches"]:
+        seed = manifest["indexes"][run["index"]]["seed_length"]
+        depth = seed + extra
+        ix = cache.get(run["index"])
+        if ix is None:
+            ix = cache[run["index"]] = EmuIndex(GOLD / f"{run['index']}.awfmi").set_seed_depth(depth)
+        klist = run_klist(run)
+        used += min(klist) >= depth
+        got = {}
+        for seg, n in _segments(run):
+            out, stats = ix.min_unique_segment(seg.data, n, klist, run["range"], run.get("initial", 0),
+                                               not run.get("norc", False), 0)
+            assert stats[3] == 0 and stats[4] == -1, (run["id"], stats)
+            got.setdefault(seg.id, []).append(out)
+        for sid, parts in got.items():
+            want = golden_searches[f"run{run['id']}|{sid.decode()}"]
+            arr = np.concatenate(parts)
+            bad = np.nonzero(arr != want)[0]
+            assert bad.size == 0, (extra, run, sid, bad[:10], arr[bad[:10]], want[bad[:10]])
+    assert used >= 10
+
+
+def test_derived_seed_table_entries_equal_counts():
+    """Every entry of the derived table is the SA interval of its d-mer: length == occurrence count."""
+    ix = EmuIndex(GOLD / "quirk_s4.awfmi").set_seed_depth(7)
+    o = ora.OracleIndex(GOLD / "quirk_s4.awfmi")
+    seq = dict(ora.fasta_records(GOLD / "quirk.fa"))[b"chr1"][:1500]
+    # a 7-mer search seeded at depth 7 reports G == 7 exactly where the 7-mer is unique on the forward strand
+    idx = np.arange(0, len(seq) - 7)
+    cnt = o.count(seq, idx, np.full(idx.size, 7))
+    out, _ = ix.min_unique_segment(seq, len(seq) - 6, [7, 7], True, use_rc=False, algo=0)
+    clean = np.array([all(c in b"ACGTacgt" for c in seq[i:i + 7]) for i in idx])
+    assert np.array_equal((out[:idx.size] == 7)[clean], (cnt == 1)[clean])
+
+
+def test_rc_seed_key_bit_trick():
+    import ctypes as C
+    from hostemu import lib
+    L = lib()
+    L.emu_rc_seed_key.restype = C.c_uint32
+    L.emu_rc_seed_key.argtypes = [C.c_uint32, C.c_uint32]
+    rng = np.random.default_rng(5)
+    for sl in range(1, 17):
+        for _ in range(50):
+            letters = rng.integers(0, 4, sl)
+            key = 0
+            for c in letters:
+                key = (key << 2) | int(c)
+            want = 0
+            for j, c in enumerate(letters):   # c[i] least significant, complemented
+                want |= (3 - int(c)) << (2 * j)
+            assert L.emu_rc_seed_key(key, sl) == want

@@ -206,6 +206,8 @@ def main():
     ap.add_argument("--cpu-sample", type=int, default=int(os.environ.get("NEWMAP_B200_CPU_SAMPLE", "1000000")))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--algo", default="auto")
+    ap.add_argument("--e2e-depth", type=int, default=int(os.environ.get("NEWMAP_B200_E2E_DEPTH", "4")),
+                    help="workspaces (streams) the end-to-end arm pipelines over")
     args = ap.parse_args()
 
     rank = int(os.environ.get("RANK", "0"))
@@ -308,7 +310,7 @@ def main():
     ms_value = ev0.elapsed_time(ev1)
 
     # ---- end-to-end arm: pinned host in, pinned host out, 3 workspaces with their own streams
-    depth = 3
+    depth = max(1, args.e2e_depth)
     slots = [(_lib.Workspace(index, max_len), _lib.PinnedBuffer(max_len)) for _ in range(depth)]
 
     def step_e2e(verify=False):
@@ -407,7 +409,7 @@ def main():
             "e2e": {"value": positions_all * args.steps / (ms_e2e * 1e-3), "unit": "positions/s",
                     "h2d_bytes_per_step": int(sum(len(s.data) for s, _ in segs)),
                     "d2h_bytes_per_step": int(positions_per_step), "ms_per_step": ms_e2e / args.steps,
-                    "timing": "host clock bracketed by device synchronize; 3 pipelined workspaces"},
+                    "timing": f"host clock bracketed by device synchronize; {depth} pipelined workspaces"},
             "gpu_launches": int(sum(s["launches"] for s in stats)),
             "clocks": clocks.summary(),
             "roofline": {"bound": "hbm", "kernel": "k_free_chain (pass 1: every position, depth-capped)",

@@ -108,6 +108,7 @@ constexpr uint32_t kInf = 0xFFFFFFFFu;       // R: other strand still present at
 constexpr uint32_t kPending = 0xFFFFFFFEu;   // G/R: to be computed by the generic kernel
 constexpr uint32_t kDeep = 0xFFFFFFFDu;      // G/R: undecided at the depth cap of the first pass
 constexpr uint32_t kNoBarrier = 0xFFFFFFFFu;
+constexpr uint32_t kCertOwnChains = 1;      // chains of their own a certificate thread may run for positions no bound settles
 constexpr uint32_t kTile = 64;               // nb[] tile (positions per thread of nb_tile_thread)
 
 // counters[] slots
@@ -646,16 +647,40 @@ NM_HD void free_cert_thread(const DevIndex &ix, const uint32_t *C32, const SegPa
       if (P.G[e] == kDeep) { e0 = e; if (!emin) emin = e; }
     if (e0) {
       const ChainResult r = run_fwd_chain(ix, C32, P, e0, P.kmax + (e0 - emin), steps, seeds);
+      // nu: the deepest explored length at which seg[e0-nu, e0) still occurs at least twice (e0 was kDeep, so the
+      // chain got beyond the first pass's cap before it could hit)
+      const uint32_t nu = r.d_hit ? r.d_hit - 1u : r.d_stop;
+      uint32_t budget = kCertOwnChains;
       for (uint32_t e = emin; e <= e0; ++e) {
         if (P.G[e] != kDeep) continue;
         const uint32_t dt = e0 - e;
-        if (r.wall && r.d_stop <= dt) continue;          // e lies beyond the wall e0's chain ran into
         uint32_t L = P.kmax;                             // deepest length e itself may be asked about
-        if (r.wall && r.d_stop - dt < L) L = r.d_stop - dt;
+        if (r.wall && r.d_stop > dt && r.d_stop - dt < L) L = r.d_stop - dt;
         if (dt == 0) {
           P.G[e] = (r.d_hit && r.d_hit <= L) ? r.d_hit : kNone;
-        } else if (L + dt <= r.d_stop && (r.d_hit == 0 || r.d_hit > L + dt)) {
+          continue;
+        }
+        const bool beyond_wall = r.wall && r.d_stop <= dt;  // e lies beyond the wall e0's chain ran into
+        if (!beyond_wall && L + dt <= r.d_stop && (r.d_hit == 0 || r.d_hit > L + dt)) {
           P.G[e] = kNone;                                // seg[e-L, e0) occurs twice, so does seg[e-L, e)
+          continue;
+        }
+        // seg[e-l, e) lies inside seg[e0-nu, e0) for l <= nu - dt, so G[e] >= nu - dt + 1; and a unique suffix of
+        // length g ending at e-1 makes the suffix of length g+1 ending at e unique, so G[e] <= G[e-1] + 1.  Where the
+        // two bounds meet (a run of positions since the last difference between two copies of a repeat: G grows by
+        // one per position) the value is settled without a chain of its own.
+        // (e-1 may belong to the group on the left, whose thread may be writing it right now: what is read is either
+        // kDeep or a final value, both are safe; only the number of chains run depends on the timing)
+        if (!beyond_wall && nu >= dt) {
+          const uint32_t left = P.G[e - 1];
+          if (left != kNone && left != kDeep && left != kPending && left + 1u == nu - dt + 1u) {
+            P.G[e] = left + 1u;
+            continue;
+          }
+        }
+        if (budget) {                                    // else: left kDeep for the third pass
+          --budget;
+          P.G[e] = chain_value(P, run_fwd_chain(ix, C32, P, e, P.kmax, steps, seeds), P.kmax, kNone);
         }
       }
     }
@@ -670,17 +695,34 @@ NM_HD void free_cert_thread(const DevIndex &ix, const uint32_t *C32, const SegPa
       if (P.R[i] == kDeep) { if (i0 == kNoBarrier) i0 = i; imax = i; }
     if (i0 != kNoBarrier) {
       const ChainResult r = run_rc_chain(ix, C32, P, i0, P.kmax + (imax - i0), steps, seeds);
-      for (uint32_t i = i0; i <= imax; ++i) {
-        if (P.R[i] != kDeep) continue;
-        const uint32_t dt = i - i0;
-        if (r.wall && r.d_stop <= dt) continue;
-        uint32_t L = P.kmax;
-        if (r.wall && r.d_stop - dt < L) L = r.d_stop - dt;
-        if (dt == 0) {
-          P.R[i] = (r.d_hit && r.d_hit <= L) ? r.d_hit : kInf;
-        } else if (L + dt <= r.d_stop && (r.d_hit == 0 || r.d_hit > L + dt)) {
-          P.R[i] = kInf;                                 // rc(seg[i0, i+L)) still occurs, so does rc(seg[i, i+L))
+      const uint32_t nu = r.d_hit ? r.d_hit - 1u : r.d_stop;  // rc(seg[i0, i0+nu)) still occurs
+      uint32_t budget = kCertOwnChains;
+      for (uint32_t i = imax;; --i) {                    // right to left: R[i] <= R[i+1] + 1
+        if (P.R[i] == kDeep) {
+          const uint32_t dt = i - i0;
+          uint32_t L = P.kmax;
+          if (r.wall && r.d_stop > dt && r.d_stop - dt < L) L = r.d_stop - dt;
+          const bool beyond_wall = r.wall && r.d_stop <= dt;
+          if (dt == 0) {
+            P.R[i] = (r.d_hit && r.d_hit <= L) ? r.d_hit : kInf;
+          } else if (!beyond_wall && L + dt <= r.d_stop && (r.d_hit == 0 || r.d_hit > L + dt)) {
+            P.R[i] = kInf;                               // rc(seg[i0, i+L)) still occurs, so does rc(seg[i, i+L))
+          } else {
+            bool done = false;
+            if (!beyond_wall && nu >= dt && i + 1 < P.seg_len) {
+              const uint32_t right = P.R[i + 1];
+              if (right != kInf && right != kDeep && right != kPending && right + 1u == nu - dt + 1u) {
+                P.R[i] = right + 1u;
+                done = true;
+              }
+            }
+            if (!done && budget) {
+              --budget;
+              P.R[i] = chain_value(P, run_rc_chain(ix, C32, P, i, P.kmax, steps, seeds), P.kmax, kInf);
+            }
+          }
         }
+        if (i == i0) break;
       }
     }
   }

@@ -552,7 +552,7 @@ int nm_workspace_search(nm_workspace *ws, uint64_t num_kmers, int mode, const ui
     const uint32_t sl = P.sl;
     P.dcap = ws->opt_dcap ? ws->opt_dcap : (deep ? sl + 8 : sl + 12);
     if (P.dcap <= sl) P.dcap = sl + 1;
-    P.gsize = ws->opt_gsize ? ws->opt_gsize : 32;
+    P.gsize = ws->opt_gsize ? ws->opt_gsize : 16;
   }
   ws->algo_req = algo;
   ws->have_search = true;

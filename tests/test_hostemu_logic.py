@@ -201,3 +201,46 @@ def test_rc_seed_key_bit_trick():
             for j, c in enumerate(letters):   # c[i] least significant, complemented
                 want |= (3 - int(c)) << (2 * j)
             assert L.emu_rc_seed_key(key, sl) == want
+
+
+def test_diverged_repeats_interpolation_certificate(tmp_path):
+    """Copies of a repeat that differ at a few positions (forward and reverse-complement copies, two and three
+    copies): between two differences the shortest unique length grows by one per position, which the certificate
+    pass settles from one chain per group plus the neighbour's value.  Every cap / group size gives the oracle's bytes."""
+    if not ora.ref_available():
+        pytest.skip("needs oracle/_ref to build fresh indexes")
+    rng = np.random.default_rng(77)
+    comp = np.zeros(256, dtype=np.uint8)
+    comp[list(b"ACGT")] = list(b"TGCA")
+    for trial in range(4):
+        n = 6000
+        a = np.frombuffer(b"ACGT", dtype=np.uint8)[rng.integers(0, 4, n)].copy()
+        unit = a[100:700].copy()
+
+        def mutate(u, every):
+            u = u.copy()
+            for pos in range(int(rng.integers(5, every)), u.size, every):
+                u[pos] = (b"ACGT".replace(bytes([u[pos]]), b""))[int(rng.integers(0, 3))]
+            return u
+        a[1500:2100] = mutate(unit, 90)                       # second copy, a difference every 90
+        a[3000:3600] = mutate(unit, 37)                       # third copy, other differences
+        a[4200:4800] = comp[mutate(unit, 55)][::-1]           # reverse-complement copy
+        if trial % 2:
+            a[5000:5005] = ord("N")
+        fa = tmp_path / f"d{trial}.fa"
+        fa.write_bytes(b">s\n" + a.tobytes() + b"\n")
+        seed = 3 + trial
+        ixp = tmp_path / f"d{trial}.awfmi"
+        ora.ref_build_index(fa, ixp, 8, seed)
+        o, e = ora.OracleIndex(ixp), EmuIndex(ixp)
+        if trial >= 2:
+            e.set_seed_depth(seed + 2)
+        klist = list(range(seed + 2, 121))
+        for batch in (n, 1000):
+            for seg in ora.segments(fa, batch, max(klist) - 1):
+                m = len(seg.data) if seg.epilogue else len(seg.data) - (max(klist) - 1)
+                want = o.min_unique_segment(seg.data, m, klist, True, nthreads=1)
+                for dcap_extra, gsize in ((1, 32), (3, 8), (2, 64), (6, 5), (1, 1)):
+                    got, st = e.min_unique_segment(seg.data, m, klist, True, algo=0, dcap=seed + 2 + dcap_extra, gsize=gsize)
+                    bad = np.nonzero(got != want)[0]
+                    assert bad.size == 0, (trial, batch, dcap_extra, gsize, bad[:10], got[bad[:10]], want[bad[:10]])

@@ -412,7 +412,7 @@ def main():
                     "timing": f"host clock bracketed by device synchronize; {depth} pipelined workspaces"},
             "gpu_launches": int(sum(s["launches"] for s in stats)),
             "clocks": clocks.summary(),
-            "roofline": {"bound": "hbm", "kernel": "k_free_chain (pass 1: every position, depth-capped)",
+            "roofline": {"bound": "hbm", "kernel": "k_pass1_tiled (pass 1 of the trajectory-free search: every position, depth-capped)",
                          "achieved": achieved, "peak": hbm_peak,
                          "unit": "GB/s", "frac": (achieved / hbm_peak) if achieved else None, "peak_source": peak_src,
                          "traffic": traffic,

@@ -148,6 +148,46 @@ int nm_workspace_option(nm_workspace *ws, int option, uint64_t value);
  * device-resident runs that never copy the output back). */
 int nm_workspace_checksum(nm_workspace *ws, uint64_t *sum);
 
+/* ---- FASTA ingest on the device (replaces newmap/fasta.py:20-190 sequence_segments for the plain-text case) ------
+ * The raw text of a FASTA file is copied to the GPU as it is read (pinned staging, several reader threads), and
+ * parsed there: header lines (first byte '>' or ';' at a line start) are located, newlines and header lines are
+ * removed by a stream compaction, and every record becomes a contiguous run of bases in device memory.  Search
+ * workspaces then take their segment windows straight from that memory (nm_workspace_attach): no per-segment
+ * host->device copy, no host-side parsing.  Semantics are those of the reference's reader: a record's id is the
+ * first whitespace-delimited token of its header line without the first byte, its bases are the other lines
+ * right-stripped and concatenated.  Right-stripping is only implemented for '\n' line ends: if a sequence line
+ * holds any other white space (space, tab, CR, VT, FF) nm_fasta_finish reports odd_whitespace = 1 and the caller
+ * must use its own reader (newmap_b200/fasta.py does). */
+typedef struct nm_fasta nm_fasta;
+typedef struct nm_fasta_info {
+  uint64_t raw_bytes;       /* text bytes received */
+  uint64_t sequence_bytes;  /* bases kept (all records) */
+  uint64_t records;         /* records, including a leading one without header line if the text starts with bases */
+  uint32_t odd_whitespace;  /* 1: white space other than '\n' inside sequence lines -- results of this parse are not usable */
+  uint32_t reserved;
+  float ms_parse;           /* device time of the parse */
+  float reserved2;
+} nm_fasta_info;
+typedef struct nm_fasta_record {
+  uint64_t seq_offset;      /* first base of the record in the device sequence buffer */
+  uint64_t seq_length;
+  uint64_t header_offset;   /* header line (without its newline) in the packed header text, nm_fasta_headers() */
+  uint64_t header_length;   /* 0 for a leading record without header line */
+} nm_fasta_record;
+int nm_fasta_open(int device, uint64_t size_hint, nm_fasta **out);
+void nm_fasta_close(nm_fasta *fa);
+/* appends n bytes of text (any host memory) */
+int nm_fasta_feed(nm_fasta *fa, const void *data, uint64_t n);
+/* appends a whole plain-text file, read by `threads` reader threads (0 = 4) straight into pinned staging */
+int nm_fasta_feed_file(nm_fasta *fa, const char *path, uint32_t threads);
+int nm_fasta_finish(nm_fasta *fa, nm_fasta_info *info);
+int nm_fasta_records(const nm_fasta *fa, nm_fasta_record *out, uint64_t capacity);      /* fills min(records, capacity) */
+int nm_fasta_headers(const nm_fasta *fa, char *out, uint64_t capacity, uint64_t *needed); /* packed header lines */
+/* copies bases [seq_offset, seq_offset + n) of the device sequence buffer to host memory (error messages, tests) */
+int nm_fasta_read(const nm_fasta *fa, uint64_t seq_offset, uint64_t n, uint8_t *out);
+/* the workspace's next search reads its segment from the parsed sequence buffer instead of an uploaded one */
+int nm_workspace_attach(nm_workspace *ws, const nm_fasta *fa, uint64_t seq_offset, uint64_t seg_len);
+
 /* Pinned host memory for segment / output staging (cudaHostAlloc / cudaFreeHost). */
 void *nm_host_alloc(uint64_t bytes);
 void nm_host_free(void *p);

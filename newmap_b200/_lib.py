@@ -40,6 +40,17 @@ class Stats(C.Structure):
         return {name: getattr(self, name) for name, _ in self._fields_}
 
 
+class FastaInfo(C.Structure):
+    _fields_ = [("raw_bytes", C.c_uint64), ("sequence_bytes", C.c_uint64), ("records", C.c_uint64),
+                ("odd_whitespace", C.c_uint32), ("reserved", C.c_uint32), ("ms_parse", C.c_float),
+                ("reserved2", C.c_float)]
+
+
+class FastaRecord(C.Structure):
+    _fields_ = [("seq_offset", C.c_uint64), ("seq_length", C.c_uint64), ("header_offset", C.c_uint64),
+                ("header_length", C.c_uint64)]
+
+
 # every symbol include/newmap_b200.h declares: (restype, argtypes)
 _vp, _u64, _u32, _i = C.c_void_p, C.c_uint64, C.c_uint32, C.c_int
 SIGNATURES = {
@@ -61,6 +72,15 @@ SIGNATURES = {
     "nm_workspace_sync": (_i, [_vp, C.POINTER(Stats)]),
     "nm_workspace_option": (_i, [_vp, _i, _u64]),
     "nm_workspace_checksum": (_i, [_vp, C.POINTER(_u64)]),
+    "nm_fasta_open": (_i, [_i, _u64, C.POINTER(_vp)]),
+    "nm_fasta_close": (None, [_vp]),
+    "nm_fasta_feed": (_i, [_vp, _vp, _u64]),
+    "nm_fasta_feed_file": (_i, [_vp, C.c_char_p, _u32]),
+    "nm_fasta_finish": (_i, [_vp, C.POINTER(FastaInfo)]),
+    "nm_fasta_records": (_i, [_vp, C.POINTER(FastaRecord), _u64]),
+    "nm_fasta_headers": (_i, [_vp, _vp, _u64, C.POINTER(_u64)]),
+    "nm_fasta_read": (_i, [_vp, _u64, _u64, _vp]),
+    "nm_workspace_attach": (_i, [_vp, _vp, _u64, _u64]),
     "nm_host_alloc": (_vp, [_u64]),
     "nm_host_free": (None, [_vp]),
     "nm_index_build": (_i, [_vp, _u64, _vp, _u64, _vp, _u64, _u32, _u32, _i, C.c_char_p, C.POINTER(C.c_double)]),
@@ -253,6 +273,13 @@ class Workspace:
         check(load().nm_workspace_option(self._h, {"ref_lf": 1, "dcap": 2, "gsize": 3, "pass1": 4}[name], int(value)),
               "nm_workspace_option")
 
+    def attach(self, fasta: "Fasta", seq_offset: int, seg_len: int):
+        """The next search reads its segment from the parsed FASTA on the device (no host->device copy)."""
+        rc = load().nm_workspace_attach(self._h, fasta._h, int(seq_offset), int(seg_len))
+        if rc == NM_EARG:
+            raise ValueError("segment outside the parsed sequence, longer than the workspace, or another device")
+        check(rc, "nm_workspace_attach")
+
     def upload(self, seg_ptr: int, seg_len: int):
         check(load().nm_workspace_upload(self._h, seg_ptr, int(seg_len)), "nm_workspace_upload")
 
@@ -279,6 +306,67 @@ class Workspace:
         v = _u64(0)
         check(load().nm_workspace_checksum(self._h, C.byref(v)), "nm_workspace_checksum")
         return v.value
+
+
+class Fasta:
+    """The text of a FASTA file parsed on the GPU (nm_fasta_*): records = [(header line bytes, offset, length)] into
+    one device buffer of bases that workspaces read in place (Workspace.attach)."""
+
+    def __init__(self, device: int | None = None, size_hint: int = 0):
+        if device is None:
+            device = int(os.environ.get("NEWMAP_B200_DEVICE", os.environ.get("LOCAL_RANK", "0")))
+        h = _vp()
+        check(load().nm_fasta_open(int(device), int(size_hint), C.byref(h)), "nm_fasta_open")
+        self._h = h
+        self.device = device
+        self.info = None
+        self.records: list = []
+
+    def feed(self, data) -> None:
+        a = as_u8(data)
+        check(load().nm_fasta_feed(self._h, a.ctypes.data, a.size), "nm_fasta_feed")
+
+    def feed_file(self, path, threads: int = 0) -> None:
+        check(load().nm_fasta_feed_file(self._h, os.fsencode(str(path)), int(threads)), f"nm_fasta_feed_file({path})")
+
+    def finish(self) -> "Fasta":
+        L = load()
+        info = FastaInfo()
+        check(L.nm_fasta_finish(self._h, C.byref(info)), "nm_fasta_finish")
+        self.info = info
+        n = int(info.records)
+        recs = (FastaRecord * max(n, 1))()
+        check(L.nm_fasta_records(self._h, recs, n), "nm_fasta_records")
+        need = _u64(0)
+        check(L.nm_fasta_headers(self._h, None, 0, C.byref(need)), "nm_fasta_headers")
+        text = C.create_string_buffer(max(int(need.value), 1))
+        check(L.nm_fasta_headers(self._h, text, need.value, None), "nm_fasta_headers")
+        raw = text.raw[:need.value]
+        self.records = [(raw[r.header_offset:r.header_offset + r.header_length], int(r.seq_offset), int(r.seq_length))
+                        for r in recs[:n]]
+        return self
+
+    def read(self, offset: int, n: int) -> bytes:
+        out = np.empty(max(int(n), 1), dtype=np.uint8)
+        check(load().nm_fasta_read(self._h, int(offset), int(n), out.ctypes.data), "nm_fasta_read")
+        return out[:n].tobytes()
+
+    def close(self):
+        if getattr(self, "_h", None):
+            load().nm_fasta_close(self._h)
+            self._h = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 class PinnedBuffer:

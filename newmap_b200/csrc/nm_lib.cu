@@ -12,6 +12,7 @@
 #include <vector>
 
 #include "../../include/newmap_b200.h"
+#include "nm_fasta.cuh"
 #include "nm_kernels.cuh"
 
 namespace {
@@ -53,6 +54,7 @@ struct nm_workspace {
   uint64_t max_seg_len = 0;
   // device buffers
   uint8_t *d_seg = nullptr, *d_codes = nullptr;
+  const uint8_t *seg_ext = nullptr;  // segment attached from a parsed FASTA (nm_workspace_attach) instead of uploaded
   uint32_t *d_seedkey = nullptr, *d_nb = nullptr, *d_tile_first = nullptr, *d_G = nullptr, *d_R = nullptr;
   void *d_out = nullptr;
   uint32_t *d_klist = nullptr;
@@ -313,6 +315,10 @@ int run_search(nm_workspace *ws, int algo) {
 
 }  // namespace
 
+void nm_internal_set_cuda_error(const char *what, const char *message) {
+  g_cuda_error = std::string(what) + ": " + message;
+}
+
 extern "C" {
 
 int nm_abi_version(void) { return NM_ABI_VERSION; }
@@ -333,6 +339,7 @@ const char *nm_strerror(int code) {
 }
 
 const char *nm_last_cuda_error(void) { return g_cuda_error.c_str(); }
+
 
 int nm_device_count(void) {
   int n = 0;
@@ -476,6 +483,23 @@ int nm_workspace_upload(nm_workspace *ws, const uint8_t *seg, uint64_t seg_len) 
   NM_CUDA(cudaEventRecord(ws->ev[EV_H2D0], ws->stream));
   if (seg_len) NM_CUDA(cudaMemcpyAsync(ws->d_seg, seg, seg_len, cudaMemcpyHostToDevice, ws->stream));
   ws->seg_len = seg_len;
+  ws->seg_ext = nullptr;
+  ws->timed_h2d = true;
+  ws->have_search = false;
+  return NM_OK;
+}
+
+int nm_workspace_attach(nm_workspace *ws, const nm_fasta *fa, uint64_t seq_offset, uint64_t seg_len) {
+  if (!ws || !fa) return NM_EARG;
+  uint64_t total = 0;
+  int device = -1;
+  const uint8_t *seq = nm_fasta_device_sequence(fa, &total, &device);
+  if (!seq || device != ws->ix->device || seg_len > ws->max_seg_len || seq_offset > total || seg_len > total - seq_offset)
+    return NM_EARG;
+  NM_CUDA(cudaSetDevice(ws->ix->device));
+  NM_CUDA(cudaEventRecord(ws->ev[EV_H2D0], ws->stream));
+  ws->seg_ext = seq + seq_offset;
+  ws->seg_len = seg_len;
   ws->timed_h2d = true;
   ws->have_search = false;
   return NM_OK;
@@ -521,7 +545,7 @@ int nm_workspace_search(nm_workspace *ws, uint64_t num_kmers, int mode, const ui
     NM_CUDA(cudaMemcpyAsync(ws->d_klist, klist, (size_t)nk * 4, cudaMemcpyHostToDevice, ws->stream));
   }
   nm::SegParams &P = ws->P;
-  P.seg = ws->d_seg;
+  P.seg = ws->seg_ext ? ws->seg_ext : ws->d_seg;
   P.codes = ws->d_codes;
   P.seedkey = ws->d_seedkey;
   P.nb = ws->d_nb;

@@ -121,3 +121,21 @@ def sequence_segments(fasta_file: BinaryIO, sequence_length: int,
             buf.clear()
             emitted_any = False
             held = None
+
+
+def window_plan(record_length: int, sequence_length: int, sequence_overlap_length: int = 0) -> list:
+    """[(start, length, epilogue)] of the segments `sequence_segments` cuts from a record of `record_length` bases --
+    the same windows in closed form, for the device ingest path where a record is already one contiguous buffer."""
+    step = sequence_length - sequence_overlap_length
+    if step <= 0:
+        raise ValueError("sequence_length must exceed sequence_overlap_length")
+    L = record_length
+    whole = 0 if L < sequence_length else (L - sequence_length) // step + 1
+    left = L - whole * step                                 # bytes in the buffer after the last whole window was cut
+    remaining_new = left - (sequence_overlap_length if whole else 0)
+    plan = [(w * step, sequence_length, False) for w in range(whole)]
+    if remaining_new > 0:
+        plan.append((whole * step, left, True))
+    elif plan:
+        plan[-1] = (plan[-1][0], sequence_length, True)
+    return plan

@@ -13,6 +13,7 @@ accepted and ignored.  There is no CPU fallback.
 from __future__ import annotations
 
 import os
+import sys
 from collections import deque
 from contextlib import ExitStack
 from dataclasses import dataclass, field
@@ -25,7 +26,7 @@ import numpy as np
 
 from . import _lib
 from .count import open_index
-from .fasta import SequenceSegment, sequence_segments
+from .fasta import SequenceSegment, sequence_segments, window_plan
 from .util import INDEX_EXTENSION, optional_gzip_open, verbose_print
 
 KMER_RANGE_SEPARATOR = ":"
@@ -37,6 +38,11 @@ COMPLEMENT_TRANSLATE_TABLE = bytes.maketrans(b"ACGTacgt", b"TGCAtgca")
 ALLOWED_BASES = b"ACGTactg"          # sic (search.py:23): the set is right, the order is not
 UNIQUE_COUNT_FILENAME_FORMAT = "{}.unique.{}"
 PIPELINE_DEPTH = int(os.environ.get("NEWMAP_B200_PIPELINE", "3"))
+DEVICE_PIPELINE_DEPTH = int(os.environ.get("NEWMAP_B200_DEVICE_PIPELINE", "4"))
+# "device": the FASTA text is parsed on the GPU (nm_fasta_*) and segments are searched where they lie;
+# "host": newmap_b200/fasta.py cuts the segments and every segment is uploaded.  Default: device unless --verbose
+# (the per-sequence statistics of the verbose log need the segment bytes on the host).
+INGEST = os.environ.get("NEWMAP_B200_INGEST", "auto")
 
 
 def nil_search_log(*_: str):
@@ -240,6 +246,9 @@ def write_unique_counts(config: SearchConfig):
     ix = open_index(config.fmindex_filepaths[0], config.device)
     lookahead_length = max_kmer_length - 1
     requested_sequence_length = config.kmer_batch_size + lookahead_length
+    if INGEST == "device" or (INGEST == "auto" and not config.verbose):
+        if _write_unique_counts_device(config, ix, data_type, unique_count_suffix):
+            return
     slots: list[_Slot] = []
     inflight: deque = deque()
     totals = dict(ambiguous=0, unique=0, none=0, max_len=min_kmer_length, min_len=max_kmer_length)
@@ -338,6 +347,165 @@ def write_unique_counts(config: SearchConfig):
         elif config.exclude_sequence_ids:
             raise ValueError("The excluded sequences were too strict and nothing was processed: "
                              f"{config.exclude_sequence_ids}")
+
+
+def _write_unique_counts_device(config: SearchConfig, ix: _lib.Index, data_type, unique_count_suffix: str) -> bool:
+    """write_unique_counts with the FASTA parsed on the GPU: the text is streamed to the device while it is read
+    (reader threads, pinned staging), records become contiguous runs of bases there, segments are the windows
+    fasta.window_plan gives and are searched in place; results come back through pinned buffers and are written by a
+    small pool of writer threads.  Returns False (nothing written) when the text needs the host reader."""
+    from concurrent.futures import ThreadPoolExecutor
+    max_kmer_length = max(config.kmer_lengths)
+    lookahead_length = max_kmer_length - 1
+    requested_sequence_length = config.kmer_batch_size + lookahead_length
+    path = Path(config.fasta_filepaths[0])
+    import time
+    trace = os.environ.get("NEWMAP_B200_TRACE")
+    t_start = time.perf_counter()
+    marks = []
+
+    def mark(name):
+        if trace:
+            marks.append((name, time.perf_counter() - t_start))
+    fa = _lib.Fasta(ix.device, size_hint=path.stat().st_size if path.suffix != ".gz" else 0)
+    mark("fasta_open")
+    itemsize = data_type.itemsize
+    slots: list = []
+    # workspaces and pinned output buffers are allocated while the file is being read
+    maker = ThreadPoolExecutor(max_workers=1)
+    made = maker.submit(lambda: [_DeviceSlot(ix, requested_sequence_length, itemsize)
+                                 for _ in range(DEVICE_PIPELINE_DEPTH + 2)])
+    try:
+        if path.suffix == ".gz":
+            with optional_gzip_open(path, "rb") as fh:
+                while True:
+                    block = fh.read(64 << 20)
+                    if not block:
+                        break
+                    fa.feed(block)
+        else:
+            fa.feed_file(path)
+        mark("text_on_device")
+        try:
+            fa.finish()
+            mark(f"parsed_{fa.info.ms_parse:.1f}ms_device")
+        except RuntimeError:
+            return False            # e.g. more header lines than the device parser handles
+        if fa.info.odd_whitespace:
+            return False            # right-stripping beyond newlines: the host reader implements it
+        slots = made.result()
+        mark("slots_ready")
+        sharded = config.world_size > 1
+        if not 0 <= config.rank < config.world_size:
+            raise ValueError("rank must be in [0, world_size)")
+        inflight: deque = deque()
+        files: list = []
+        sequence_processed = False
+        current_sequence_id = None
+        current_fd = -1
+        segment_number = -1
+        segment_in_sequence = 0
+
+        def write_out(slot, fd, nbytes, offset, truncate_to):
+            os.pwrite(fd, memoryview(slot.out.array)[:nbytes], offset)
+            if truncate_to is not None:
+                os.ftruncate(fd, truncate_to)
+
+        def finish(slot):
+            (seq_off, seg_len, num_kmers, fd, offset, epilogue) = slot.job
+            st = slot.ws.sync()
+            if st.zero_pos >= 0:
+                _raise_zero_count(fa.read(seq_off, seg_len), st)
+            slot.pending = pool.submit(write_out, slot, fd, num_kmers * itemsize, offset * itemsize,
+                                       (offset + num_kmers) * itemsize if epilogue else None)
+            slot.job = None
+
+        with ThreadPoolExecutor(max_workers=3) as pool:
+            try:
+                for header, rec_off, rec_len in fa.records:
+                    tokens = header.split()
+                    seq_id = tokens[0][1:] if tokens else b""       # fasta.py:60-75
+                    if rec_len == 0:
+                        continue
+                    if current_sequence_id != seq_id:
+                        if config.include_sequence_ids or config.exclude_sequence_ids:   # search.py:268-278, quirk included
+                            if (seq_id not in config.include_sequence_ids) or (seq_id in config.exclude_sequence_ids):
+                                continue
+                        sequence_processed = True
+                        current_sequence_id = seq_id
+                        out_path = config.output_directory / UNIQUE_COUNT_FILENAME_FORMAT.format(
+                            seq_id.decode(), unique_count_suffix)
+                        flags = os.O_RDWR | os.O_CREAT | (0 if sharded else os.O_TRUNC)
+                        current_fd = os.open(out_path, flags, 0o644)
+                        files.append(current_fd)
+                        segment_in_sequence = 0
+                    for start, length, epilogue in window_plan(rec_len, requested_sequence_length, lookahead_length):
+                        num_kmers = length if epilogue else length - lookahead_length
+                        segment_number += 1
+                        offset = segment_in_sequence * config.kmer_batch_size
+                        segment_in_sequence += 1
+                        if segment_number % config.world_size != config.rank:
+                            continue
+                        if len(inflight) >= DEVICE_PIPELINE_DEPTH:
+                            finish(inflight.popleft())
+                        slot = next((s for s in slots if s.job is None and (s.pending is None or s.pending.done())), None)
+                        if slot is None:
+                            slot = next(s for s in slots if s.job is None)
+                        if slot.pending is not None:
+                            slot.pending.result()
+                            slot.pending = None
+                        slot.job = (rec_off + start, length, num_kmers, current_fd, offset, epilogue)
+                        slot.ws.attach(fa, rec_off + start, length)
+                        slot.ws.search(num_kmers, config.kmer_lengths, config.is_binary_search,
+                                       config.initial_search_length, config.use_reverse_complement, config.algorithm,
+                                       itemsize)
+                        slot.ws.download(slot.out.ptr)
+                        inflight.append(slot)
+                mark("all_segments_launched")
+                while inflight:
+                    finish(inflight.popleft())
+                mark("all_segments_searched")
+                for s_ in slots:
+                    if s_.pending is not None:
+                        s_.pending.result()
+                mark("all_written")
+            finally:
+                pool.shutdown(wait=True)
+                for fd in files:
+                    os.close(fd)
+        if not sequence_processed:
+            if config.include_sequence_ids:
+                raise ValueError(f"None of the included sequences were found: {config.include_sequence_ids}")
+            elif config.exclude_sequence_ids:
+                raise ValueError("The excluded sequences were too strict and nothing was processed: "
+                                 f"{config.exclude_sequence_ids}")
+        return True
+    finally:
+        try:
+            slots = slots or made.result()
+        except Exception:
+            pass
+        maker.shutdown(wait=True)
+        for s_ in slots:
+            s_.close()
+        fa.close()
+        mark("closed")
+        if trace:
+            print("[newmap_b200 ingest] " + ", ".join(f"{n} {t:.3f}s" for n, t in marks), file=sys.stderr, flush=True)
+
+
+class _DeviceSlot:
+    """One in-flight segment of the device ingest path: a workspace (stream) + pinned staging for its output."""
+
+    def __init__(self, ix: _lib.Index, max_seg_len: int, out_itemsize: int):
+        self.ws = _lib.Workspace(ix, max_seg_len)
+        self.out = _lib.PinnedBuffer(max_seg_len * out_itemsize)
+        self.job = None
+        self.pending = None
+
+    def close(self):
+        self.ws.close()
+        self.out.close()
 
 
 def print_summary_statisitcs(config, sequence_id, total_unique_lengths_count, total_ambiguous_positions,

@@ -63,6 +63,7 @@ def run(rank, world, port, fasta, index, klist, is_range, batch, outdir):
 
     search.open_index = lambda path, device=None: object()
     search._Slot = Slot
+    search.INGEST = "host"       # the host reader + per-segment upload path (the device ingest path needs a GPU)
     dist.barrier()
     search.write_unique_counts(search.SearchConfig(
         fasta_filepaths=[Path(fasta)], fmindex_filepaths=[Path(index)], kmer_lengths=list(klist),

@@ -64,3 +64,21 @@ def test_block_boundaries_and_gzip(tmp_path, monkeypatch):
     from newmap_b200.util import optional_gzip_open
     with optional_gzip_open(gz, "rb") as fh:
         assert [(s.id, s.data, s.epilogue) for s in fasta.sequence_segments(fh, 1039, 39)] == want
+
+
+def test_window_plan_is_sequence_segments_in_closed_form():
+    """fasta.window_plan (used by the device ingest path, where a record is one contiguous device buffer) cuts exactly
+    the windows sequence_segments cuts."""
+    import io
+    import numpy as np
+    from newmap_b200.fasta import sequence_segments, window_plan
+    rng = np.random.default_rng(11)
+    for _ in range(300):
+        sl = int(rng.integers(2, 60))
+        ov = int(rng.integers(0, sl))
+        L = int(rng.integers(0, 400))
+        seq = bytes(rng.integers(65, 70, L, dtype=np.uint8))
+        fa = b">r\n" + b"\n".join(seq[i:i + 17] for i in range(0, L, 17)) + b"\n"
+        want = [(s.data, s.epilogue) for s in sequence_segments(io.BytesIO(fa), sl, ov)]
+        got = [(seq[a:a + n], ep) for a, n, ep in window_plan(L, sl, ov)]
+        assert got == want, (L, sl, ov)

@@ -1,0 +1,149 @@
+"""FASTA ingest on the device (nm_fasta_*, newmap_b200.search._write_unique_counts_device) against the host reader
+(newmap_b200/fasta.py, which tests/test_fasta_segments.py pins to the reference's segmentation cases)."""
+import gzip
+import io
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLD
+from newmap_b200.fasta import _records
+
+pytestmark = pytest.mark.gpu
+
+
+def _host_records(text: bytes):
+    recs, cur, parts = [], None, []
+    for sid, piece, finished in _records(io.BytesIO(text)):
+        if cur is None:
+            cur = sid
+        parts.append(piece)
+        if finished:
+            recs.append((sid, b"".join(parts)))
+            parts, cur = [], None
+    return recs
+
+
+def _device_records(nm, text: bytes, chunks=None):
+    with nm.Fasta(0) as fa:
+        if chunks:
+            for i in range(0, len(text), chunks):
+                fa.feed(text[i:i + chunks])
+        else:
+            fa.feed(text)
+        fa.finish()
+        out = []
+        for header, off, n in fa.records:
+            tok = header.split()
+            out.append((tok[0][1:] if tok else b"", fa.read(off, n)))
+        return out, fa.info
+
+
+@pytest.fixture(scope="module")
+def nm():
+    from newmap_b200 import _lib
+    _lib.load()
+    return _lib
+
+
+def _random_fasta(rng, nrec, maxlen, width, leading=False, trailing_newline=True, blank_lines=True):
+    parts = []
+    if leading:
+        parts.append(b"ACGTNNACGT\nAC\n")
+    for r in range(nrec):
+        L = int(rng.integers(0, maxlen))
+        seq = bytes(np.frombuffer(b"ACGTNacgtn", dtype=np.uint8)[rng.integers(0, 10, L)])
+        start = b">" if r % 5 else b";"
+        parts.append(start + f"rec{r} some description {r}".encode() + b"\n")
+        for i in range(0, L, width):
+            parts.append(seq[i:i + width] + b"\n")
+            if blank_lines and rng.integers(0, 50) == 0:
+                parts.append(b"\n")
+    text = b"".join(parts)
+    return text if trailing_newline else text.rstrip(b"\n")
+
+
+def test_device_parse_equals_host_reader(nm):
+    rng = np.random.default_rng(5)
+    cases = [(3, 300, 60, False, True), (40, 20000, 61, True, False), (1, 100000, 80, False, True),
+             (200, 50, 7, True, True), (0, 1, 60, True, True), (5, 9000, 4096, False, False)]
+    for nrec, maxlen, width, leading, trailing in cases:
+        text = _random_fasta(rng, nrec, maxlen, width, leading, trailing)
+        want = [(i, s) for i, s in _host_records(text)]
+        for chunks in (None, 1000):
+            got, info = _device_records(nm, text, chunks)
+            assert info.odd_whitespace == 0 and info.raw_bytes == len(text)
+            assert [g for g in got if g[1]] == [w for w in want if w[1]], (nrec, maxlen, width, leading, trailing, chunks)
+    got, info = _device_records(nm, b"")
+    assert got == [] and info.records == 0
+    got, info = _device_records(nm, b">only header")
+    assert [g for g in got if g[1]] == []
+    # white space that needs real right-stripping is reported, not parsed
+    for text in (b">a\nACGT \nAC\n", b">a\r\nACGT\r\nAC\r\n", b">a\nAC\tGT\n"):
+        assert _device_records(nm, text)[1].odd_whitespace == 1
+
+
+def test_feed_file_reads_with_threads(nm, tmp_path):
+    rng = np.random.default_rng(9)
+    text = _random_fasta(rng, 6, 30_000_000, 60, blank_lines=False)       # > 32 MiB chunks: several readers
+    p = tmp_path / "big.fa"
+    p.write_bytes(text)
+    want = [(i, s) for i, s in _host_records(text) if s]
+    with nm.Fasta(0, size_hint=len(text)) as fa:
+        fa.feed_file(p, threads=3)
+        fa.finish()
+        assert fa.info.raw_bytes == len(text)
+        got = [(h.split()[0][1:], n) for h, off, n in fa.records if n]
+        assert got == [(i, len(s)) for i, s in want]
+        for (h, off, n), (_, s) in zip([r for r in fa.records if r[2]], want):
+            assert fa.read(off, min(n, 1000)) == s[:1000]
+            assert fa.read(off + n - min(n, 777), min(n, 777)) == s[-min(n, 777):]
+
+
+def _run_search(tmp_path, name, fasta, index, ingest, monkeypatch, **kw):
+    from pathlib import Path
+    from newmap_b200 import search as S
+    out = tmp_path / f"{name}_{ingest}"
+    out.mkdir()
+    monkeypatch.setattr(S, "INGEST", ingest)
+    S.write_unique_counts(S.SearchConfig(fasta_filepaths=[Path(fasta)], fmindex_filepaths=[Path(index)],
+                                         output_directory=out, **kw))
+    return {p.name: p.read_bytes() for p in sorted(out.iterdir())}
+
+
+@pytest.mark.parametrize("batch", [15, 1000, 10_000_000])
+def test_device_ingest_writes_the_same_files(nm, tmp_path, monkeypatch, batch):
+    for fasta, index, kl, rng_mode in (("genome.fa", "genome_s1.awfmi", list(range(4, 11)), True),
+                                       ("quirk.fa", "quirk_s6.awfmi", list(range(20, 201)), True),
+                                       ("quirk.fa", "quirk_s4.awfmi", [24, 36, 50, 100], False),
+                                       ("quirk_iupac.fa", "quirk_iupac_s5.awfmi", list(range(8, 41)), True)):
+        kw = dict(kmer_lengths=kl, is_binary_search=rng_mode, kmer_batch_size=batch)
+        a = _run_search(tmp_path, f"{fasta}{batch}{len(kl)}", GOLD / fasta, GOLD / index, "host", monkeypatch, **kw)
+        b = _run_search(tmp_path, f"{fasta}{batch}{len(kl)}", GOLD / fasta, GOLD / index, "device", monkeypatch, **kw)
+        assert a.keys() == b.keys() and a, (fasta, batch)
+        for k in a:
+            assert a[k] == b[k], (fasta, batch, k)
+
+
+def test_device_ingest_gz_filters_and_sharding(nm, tmp_path, monkeypatch):
+    gz = tmp_path / "quirk.fa.gz"
+    with gzip.open(gz, "wb") as fh:
+        fh.write((GOLD / "quirk.fa").read_bytes())
+    kw = dict(kmer_lengths=list(range(20, 101)), is_binary_search=True, kmer_batch_size=700)
+    a = _run_search(tmp_path, "gz", GOLD / "quirk.fa", GOLD / "quirk_s6.awfmi", "host", monkeypatch, **kw)
+    b = _run_search(tmp_path, "gz", gz, GOLD / "quirk_s6.awfmi", "device", monkeypatch, **kw)
+    assert a == b
+    c = _run_search(tmp_path, "inc", GOLD / "quirk.fa", GOLD / "quirk_s6.awfmi", "device", monkeypatch,
+                    include_sequence_ids=[b"chr2"], **kw)
+    assert list(c) == ["chr2.unique.uint8"] and c["chr2.unique.uint8"] == a["chr2.unique.uint8"]
+    # two ranks share the output files (host-side gather at window offsets)
+    from pathlib import Path
+    from newmap_b200 import search as S
+    out = tmp_path / "sharded"
+    out.mkdir()
+    monkeypatch.setattr(S, "INGEST", "device")
+    for rank in (1, 0):
+        S.write_unique_counts(S.SearchConfig(fasta_filepaths=[GOLD / "quirk.fa"], fmindex_filepaths=[GOLD / "quirk_s6.awfmi"],
+                                             output_directory=out, rank=rank, world_size=2, **kw))
+    assert {p.name: p.read_bytes() for p in sorted(out.iterdir())} == a

@@ -262,8 +262,12 @@ def main():
     import torch
     import torch.distributed as dist
     torch.cuda.set_device(local)
+    # rank 0 prints ONE JSON line on stdout: everything else that writes to fd 1 (NCCL's version banner is printed
+    # from C at its first collective, whatever NCCL_DEBUG says) is sent to stderr, the line goes to the saved fd
+    sys.stdout.flush()
+    json_fd = os.dup(1)
+    os.dup2(2, 1)
     if world > 1:
-        os.environ["NCCL_DEBUG"] = "WARN"      # keep NCCL's version banner off stdout: rank 0 prints ONE JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     def barrier():
@@ -471,7 +475,8 @@ def main():
                                     "kind": "reference", "sample": r["sample"], "native_share": r["native_share"],
                                     "value_raw_sample": r["value_raw_sample"],
                                     "index_reload_s_per_call": r["index_reload_s_per_call"]}
-        print(json.dumps(line), flush=True)
+        sys.stdout.flush()
+        os.write(json_fd, (json.dumps(line) + "\n").encode())
     barrier()
     if world > 1:
         dist.destroy_process_group()

@@ -1,5 +1,7 @@
 """Parity of the CUDA path (through the C-ABI, libnewmap_b200.so) with the oracle and with the
 fixtures the unmodified reference produced.  Bit-exact: all of this is integer / byte work."""
+import os
+
 import numpy as np
 import pytest
 
@@ -277,6 +279,16 @@ def test_large_segment_properties_and_cross_algorithm_checksum(nm, tmp_path):
         sub = pos[:300]
         assert np.array_equal(o.count(seg, sub, a[sub].astype(np.uint64)) + o.count(seg, sub, a[sub].astype(np.uint64), rc=True),
                               np.ones(300, dtype=np.uint32))
+        # the other BASELINE configs at full segment size, trajectory-free against the reference-trajectory kernel:
+        # explicit k list (configs[1]) and the widest range (configs[4]: k=12:255, below the derived seed depth)
+        ix.set_seed_depth(int(os.environ.get("NEWMAP_B200_TEST_DEPTH", "14")))
+        for klist, is_range in (([24, 36, 50, 100], False), (list(range(12, 256)), True)):
+            m = 2_000_000
+            sub = seq[3_000_000:3_000_000 + m + max(klist) - 1]
+            x, st_x = ix.min_unique(sub, m, klist, is_range, algo="auto")
+            y, st_y = ix.min_unique(sub, m, klist, is_range, algo="trajectory")
+            assert np.array_equal(x, y), (klist[:2], is_range, np.nonzero(x != y)[0][:10])
+            assert x.dtype == np.uint8 and st_x.lf_steps < st_y.lf_steps and x.any()
         # device-resident form: checksum computed on the GPU equals the host checksum of the bytes
         ws = nm.Workspace(ix, len(seg))
         buf = nm.PinnedBuffer(len(seg))

@@ -227,10 +227,15 @@ def main():
     ap.add_argument("--cpu-sample", type=int, default=int(os.environ.get("NEWMAP_B200_CPU_SAMPLE", "1000000")))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--algo", default="auto")
+    ap.add_argument("--k-range", default=None, help="other search range than the metric's 20:200, e.g. 12:255 "
+                    "(BASELINE configs[4]); the JSON line then says so in config.k_range")
     ap.add_argument("--e2e-depth", type=int, default=int(os.environ.get("NEWMAP_B200_E2E_DEPTH", "4")),
                     help="workspaces (streams) the end-to-end arm pipelines over")
     args = ap.parse_args()
 
+    global K_RANGE
+    if args.k_range:
+        K_RANGE = tuple(int(x) for x in args.k_range.split(":"))
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
@@ -240,6 +245,10 @@ def main():
             "config": {"workload": WORKLOADS[args.workload], "workload_id": args.workload,
                        "kmer_batch_size": BATCH, "index": f".awfmi v8 (reference format), seed {SEED_LEN}, SA ratio {SA_RATIO}",
                        "parallelism": f"index replicated x{world}, segments sharded, no collective"}}
+    if args.k_range:
+        base["metric"] = f"genome positions/sec, min-unique-k search k={args.k_range}"
+        base["config"]["k_range"] = args.k_range
+        base["config"]["workload"] = base["config"]["workload"].replace("k=20:200", f"k={args.k_range}")
 
     # ---------------- reference arm: CPU only, rank 0 only
     if args.impl == "reference":
@@ -437,7 +446,8 @@ def main():
                     "timing": f"host clock bracketed by device synchronize; {depth} pipelined workspaces"},
             "gpu_launches": int(sum(s["launches"] for s in stats)),
             "clocks": clocks.summary(),
-            "roofline": {"bound": "hbm", "kernel": "k_pass1_tiled (pass 1 of the trajectory-free search: every position, depth-capped)",
+            "roofline": {"bound": "hbm", "kernel": ("k_pass1_tiled" if iso and iso[0]["seed_depth"] >= 13 else "k_free_chain") +
+                                   " (pass 1 of the trajectory-free search: every position, depth-capped)",
                          "achieved": achieved, "peak": hbm_peak,
                          "unit": "GB/s", "frac": (achieved / hbm_peak) if achieved else None, "peak_source": peak_src,
                          "traffic": traffic,

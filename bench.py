@@ -457,7 +457,7 @@ def main():
                          "lf_steps_per_launch": lf1 / max(1, launches), "seed_lookups_per_launch": seeds1 / max(1, launches),
                          "ms_per_launch": ms_pass1 / max(1, launches),
                          "timing": "CUDA events on the workspace stream, one search at a time (no overlap)",
-                         "whole_search": {"kernels": "k_free_chain pass 1 + k_free_cert + k_free_chain pass 3",
+                         "whole_search": {"kernels": "pass 1 + k_free_cert + k_free_chain (pass 3)",
                                           "achieved": bytes_all / (ms_search * 1e-3) / 1e9 if ms_search else None,
                                           "ms_per_segment": ms_search / max(1, launches),
                                           "lf_steps_per_position": lf / max(1, positions_per_step * args.steps),

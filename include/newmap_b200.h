@@ -101,8 +101,9 @@ void nm_index_close(nm_index *ix);
 int nm_index_info_get(const nm_index *ix, nm_index_info *info);
 /* The seed table of the file (AwFmKmerTable.c:24-35, depth kmerLengthInSeedTable, 12 by default) saves the
  * first seedLen backward-extension steps of a query.  With 180 GB of HBM a DEEPER table pays: nm_index_open
- * derives one on the device from the file's table and the BWT (one extension step per entry and level; depth
- * chosen from bwtLength and free memory, at most 16 = 34 GB; NEWMAP_B200_SEED_DEPTH overrides, 0 = none) and
+ * derives one on the device from the file's table and the BWT (one extension step per entry and level; each
+ * entry holds the interval of its d-mer and of the reverse complement, 16 B; depth chosen from bwtLength and
+ * free memory, at most 16 = 69 GB; NEWMAP_B200_SEED_DEPTH overrides, 0 = none) and
  * searches whose shortest length reaches that depth start their chains from it.  This call rebuilds it at
  * another depth (<= seed length: drop it).  No search may be in flight.  Results never depend on it. */
 int nm_index_set_seed_depth(nm_index *ix, uint32_t depth);

@@ -122,12 +122,19 @@ struct alignas(8) SeedEntry32 {  // one 64-bit load
   uint32_t start, len;
 };
 
+// entry of the derived table: the SA interval of the d-mer AND of its reverse complement, so that one 16-byte
+// access seeds the forward-strand chain that ends where the d-mer ends and the other-strand chain that starts
+// where it starts
+struct alignas(16) SeedEntryPair {
+  SeedEntry32 fwd, rc;
+};
+
 struct DevIndex {
   const uint8_t *native;      // (n_blocks + 1) * 160 B, file order, one zero-plane pad block
   const uint32_t *rank32;     // (n64 + 1) * 8 u32, or nullptr
   const SeedEntry32 *seed32;  // 4^seed_len entries, or nullptr
   const uint64_t *seed64;     // 4^seed_len {start,end} pairs exactly as in the file
-  const SeedEntry32 *seedx;   // derived on the device at load time: 4^seedx_len entries of a DEEPER seed table
+  const SeedEntryPair *seedx; // derived on the device at load time: 4^seedx_len entries of a DEEPER seed table
   uint32_t seedx_len;         // (seed_len < seedx_len <= 16), or nullptr / 0
   const uint32_t *c32;        // prefixSums as u32[6] in device memory (rank32 path), or nullptr
   uint64_t C[6];              // prefixSums, AwFmCreate.c:299-305
@@ -333,7 +340,8 @@ struct SegParams {
   const uint8_t *seg;    // raw bytes, seg_len
   uint8_t *codes;        // seg_len
   uint32_t *seedkey;     // seg_len: the sl letters starting at p packed 2 bits each (valid unless codes[p] & kSeedBad)
-  const SeedEntry32 *seedtab;  // seed table the chains start from: 4^sl entries (index seed table or the deeper one)
+  const SeedEntry32 *seedtab;  // seed table the chains start from: 4^sl entries of the file's table ...
+  const SeedEntryPair *seedpair;  // ... or of the derived both-strand table (exactly one of the two is set)
   uint32_t sl;           // its depth; kmin >= sl
   uint32_t *nb;          // seg_len: position of the first barrier >= p inside p's tile, or kNoBarrier
   uint32_t *tile_first;  // ceil(seg_len / kTile): first barrier of the tile, or kNoBarrier
@@ -535,6 +543,19 @@ NM_HD bool chain_seeded(const SegParams &P, uint32_t kind, uint32_t p) {
 NM_HD uint32_t chain_seed_key(const SegParams &P, uint32_t kind, uint32_t p) {
   return kind == 0u ? P.seedkey[p - P.sl] : rc_seed_key(P.seedkey[p], P.sl);
 }
+// seed-table entry of the chain (kind, p): the window of P.sl letters ending at p (forward strand) or starting at p
+NM_HD SeedEntry32 seed_entry(const SegParams &P, uint32_t kind, uint32_t p) {
+  const uint32_t key = P.seedkey[kind == 0u ? p - P.sl : p];
+  if (P.seedpair) {
+#if defined(__CUDA_ARCH__)
+    const uint4 e = __ldg(reinterpret_cast<const uint4 *>(P.seedpair + key));
+    return kind == 0u ? SeedEntry32{e.x, e.y} : SeedEntry32{e.z, e.w};
+#else
+    return kind == 0u ? P.seedpair[key].fwd : P.seedpair[key].rc;
+#endif
+  }
+  return P.seedtab[kind == 0u ? key : rc_seed_key(key, P.sl)];
+}
 NM_HD unsigned rc_letter_of_code(uint8_t c) {
   const unsigned l = c & kLetterMask;
   if (c & kIrregular) return l == 3u ? 3u : 4u;  // U/u keeps letter t (search.py:22 does not complement it)
@@ -548,7 +569,7 @@ NM_HD ChainState chain_from_letter(const uint32_t *C32, const SegParams &P, uint
 NM_HD ChainState chain_init(const uint32_t *C32, const SegParams &P, uint32_t kind, uint32_t p, uint32_t &seeds) {
   if (chain_seeded(P, kind, p)) {
     ++seeds;
-    return chain_from_seed(P.seedtab[chain_seed_key(P, kind, p)], P.sl);
+    return chain_from_seed(seed_entry(P, kind, p), P.sl);
   }
   return chain_from_letter(C32, P, kind, p);
 }
@@ -916,6 +937,14 @@ NM_HD void seed_extend_thread(const DevIndex &ix, const uint32_t *C32, const See
     }
     dst[c * stride + key] = SeedEntry32{nhi > nlo ? C32[c] + nlo : 0u, nhi > nlo ? nhi - nlo : 0u};
   }
+}
+
+// both-strand table from the finished one-strand table of depth d: pair[key] = {t[key], t[rc(key)]}
+NM_HD void seed_pair_thread(const SeedEntry32 *t, uint32_t d, SeedEntryPair *pair, uint64_t key) {
+  SeedEntryPair e;
+  e.fwd = t[key];
+  e.rc = t[rc_seed_key((uint32_t)key, d)];
+  pair[key] = e;
 }
 
 // FNV-1a-like fold used by nm_workspace_checksum (order independent: sum of per-position hashes)

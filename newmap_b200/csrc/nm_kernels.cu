@@ -44,6 +44,11 @@ __global__ void __launch_bounds__(kBlock) k_seed_extend(DevIndex ix, const SeedE
   if (key < (1ull << (2 * d))) seed_extend_thread(ix, sC, src, d, dst, key);
 }
 
+__global__ void __launch_bounds__(kBlock) k_seed_pair(const SeedEntry32 *t, uint32_t d, SeedEntryPair *pair) {
+  const uint64_t key = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (key < (1ull << (2 * d))) seed_pair_thread(t, d, pair, key);
+}
+
 template <bool RC>
 __global__ void __launch_bounds__(kBlock) k_count(DevIndex ix, const uint8_t *seq, const uint64_t *idx,
                                                   const uint64_t *len, uint64_t n, uint32_t *counts,
@@ -176,7 +181,7 @@ constexpr int kP1Tile = 2 * kBlock;
 
 __global__ void __launch_bounds__(kBlock, 8) k_pass1_tiled(DevIndex ix, SegParams P) {
   __shared__ uint32_t sC[8];
-  __shared__ uint4 s_items[2 * kP1Tile];  // {p, lo, hi, d | kind << 31}
+  __shared__ uint4 s_items[2 * kP1Tile + 16];  // {p, lo, hi, d | kind << 31}; + the seedless ends of block 0
   __shared__ uint32_t s_count, s_next;
   if (threadIdx.x == 0) s_count = s_next = 0;
   const uint32_t *C32 = stage_c32(ix, sC);  // __syncthreads inside
@@ -184,51 +189,67 @@ __global__ void __launch_bounds__(kBlock, 8) k_pass1_tiled(DevIndex ix, SegParam
   const uint32_t t0 = blockIdx.x * kP1Tile;
   uint32_t steps = 0, seeds = 0;
 
-  // ---- phase A: the code bytes of all four chains, then their seed keys, then their table entries, each group
-  // issued together so that the loads of one group are in flight at the same time
+  // ---- phase A.  Thread work = two seed windows q (letters q .. q+sl-1); a window seeds the other-strand chain that
+  // STARTS at q and the forward-strand chain that ENDS at q + sl, so with the both-strand table one 16-byte entry
+  // serves two chains.  Code bytes first, then keys, then entries: the loads of each group are in flight together.
   SeedEntry32 ent[4];
   uint32_t st[4];  // 0 outside the segment, 1 not wanted, 2 starts from a letter, 3 starts from the seed table
   {
-    uint32_t cprev[2], cself[2], cwin[2];  // codes[p - 1], codes[p], codes[p - sl]
+    uint32_t cself[2], clast[2];  // codes[q], codes[q + sl - 1]
 #pragma unroll
     for (int j = 0; j < 2; ++j) {
-      const uint32_t p = t0 + j * kBlock + threadIdx.x;
-      cprev[j] = (p >= 1u && p <= P.seg_len) ? (uint32_t)ld8(P.codes + p - 1) : (uint32_t)kBarrier;
-      cself[j] = p < P.seg_len ? (uint32_t)ld8(P.codes + p) : (uint32_t)(kNoStart | kSeedBad);
-      cwin[j] = (p >= P.sl && p <= P.seg_len) ? (uint32_t)ld8(P.codes + p - P.sl) : (uint32_t)kSeedBad;
+      const uint32_t q = t0 + j * kBlock + threadIdx.x;
+      const uint64_t e = (uint64_t)q + P.sl;
+      cself[j] = q < P.seg_len ? (uint32_t)ld8(P.codes + q) : (uint32_t)(kNoStart | kSeedBad);
+      clast[j] = e <= P.seg_len ? (uint32_t)ld8(P.codes + e - 1) : (uint32_t)kBarrier;
     }
-    uint32_t key[4];
+    uint32_t key[2];
 #pragma unroll
-    for (int slot = 0; slot < 4; ++slot) {
-      const int j = slot >> 1;
-      const uint32_t p = t0 + j * kBlock + threadIdx.x, kind = slot & 1;
-      uint32_t v = 0;
-      if (kind == 0u) {  // fwd_wanted / chain_seeded(kind 0) on the bytes already loaded
-        if (p <= P.seg_len) v = (p >= 1u && !(cprev[j] & kBarrier)) ? ((!(cwin[j] & kSeedBad) && !(P.mode == 1 && p == P.seg_len)) ? 3u : 2u) : 1u;
-      } else {           // rc_wanted / chain_seeded(kind 1)
-        if (p < P.seg_len) v = (P.use_rc && p < P.num_kmers && !(cself[j] & kNoStart)) ? (!(cself[j] & kSeedBad) ? 3u : 2u) : 1u;
-      }
-      st[slot] = v;
-      key[slot] = v == 3u ? ld32(P.seedkey + (kind == 0u ? p - P.sl : p)) : 0u;
+    for (int j = 0; j < 2; ++j) {
+      const uint32_t q = t0 + j * kBlock + threadIdx.x;
+      const uint64_t e = (uint64_t)q + P.sl;
+      const bool window_ok = !(cself[j] & kSeedBad);
+      uint32_t v0 = 0, v1 = 0;
+      if (e <= P.seg_len)  // fwd_wanted / chain_seeded(kind 0) for end e, on the bytes already loaded
+        v0 = !(clast[j] & kBarrier) ? ((window_ok && !(P.mode == 1 && e == P.seg_len)) ? 3u : 2u) : 1u;
+      if (q < P.seg_len)   // rc_wanted / chain_seeded(kind 1) for start q
+        v1 = (P.use_rc && q < P.num_kmers && !(cself[j] & kNoStart)) ? (window_ok ? 3u : 2u) : 1u;
+      st[2 * j] = v0;
+      st[2 * j + 1] = v1;
+      key[j] = (v0 == 3u || v1 == 3u) ? ld32(P.seedkey + q) : 0u;
     }
 #pragma unroll
-    for (int slot = 0; slot < 4; ++slot) {
-      const uint32_t k = (slot & 1) ? rc_seed_key(key[slot], P.sl) : key[slot];
-      ent[slot] = SeedEntry32{0u, 0u};
-      if (st[slot] == 3u) {
-        const uint2 e = __ldg(reinterpret_cast<const uint2 *>(P.seedtab + k));
-        ent[slot] = SeedEntry32{e.x, e.y};
+    for (int j = 0; j < 2; ++j) {
+      ent[2 * j] = ent[2 * j + 1] = SeedEntry32{0u, 0u};
+      if (st[2 * j] == 3u || st[2 * j + 1] == 3u) {
+        if (P.seedpair) {
+          const uint4 e = __ldg(reinterpret_cast<const uint4 *>(P.seedpair + key[j]));
+          ent[2 * j] = SeedEntry32{e.x, e.y};
+          ent[2 * j + 1] = SeedEntry32{e.z, e.w};
+          ++seeds;
+        } else {
+          if (st[2 * j] == 3u) {
+            const uint2 e = __ldg(reinterpret_cast<const uint2 *>(P.seedtab + key[j]));
+            ent[2 * j] = SeedEntry32{e.x, e.y};
+            ++seeds;
+          }
+          if (st[2 * j + 1] == 3u) {
+            const uint2 e = __ldg(reinterpret_cast<const uint2 *>(P.seedtab + rc_seed_key(key[j], P.sl)));
+            ent[2 * j + 1] = SeedEntry32{e.x, e.y};
+            ++seeds;
+          }
+        }
       }
     }
   }
 #pragma unroll
   for (int slot = 0; slot < 4; ++slot) {
-    const uint32_t p = t0 + (slot >> 1) * kBlock + threadIdx.x, kind = slot & 1;
+    const uint32_t kind = slot & 1;
+    const uint32_t p = t0 + (slot >> 1) * kBlock + threadIdx.x + (kind == 0u ? P.sl : 0u);
     if (st[slot] == 0) continue;
     uint32_t *dst = kind == 0u ? P.G + p : P.R + p;
     const uint32_t none = kind == 0u ? kNone : kInf;
     if (st[slot] == 1) { *dst = none; continue; }
-    if (st[slot] == 3) ++seeds;
     const ChainState s = st[slot] == 3 ? chain_from_seed(ent[slot], P.sl) : chain_from_letter(C32, P, kind, p);
     ChainResult r{0, 0, false};
     if (chain_finished(P, kind, s, r)) {
@@ -236,6 +257,22 @@ __global__ void __launch_bounds__(kBlock, 8) k_pass1_tiled(DevIndex ix, SegParam
     } else {
       const uint32_t at = atomicAdd(&s_count, 1u);
       s_items[at] = make_uint4(p, s.lo, s.hi, s.d | (kind << 31));
+    }
+  }
+  // forward-strand chains that end before the first whole window (e < sl) have no seed: the first block takes them
+  if (blockIdx.x == 0 && threadIdx.x < P.sl && threadIdx.x <= P.seg_len) {
+    const uint32_t e = threadIdx.x;
+    if (fwd_wanted(P, e)) {
+      const ChainState s = chain_from_letter(C32, P, 0u, e);
+      ChainResult r{0, 0, false};
+      if (chain_finished(P, 0u, s, r)) {
+        P.G[e] = chain_value(P, r, cap, kNone);
+      } else {
+        const uint32_t at = atomicAdd(&s_count, 1u);
+        s_items[at] = make_uint4(e, s.lo, s.hi, s.d);
+      }
+    } else {
+      P.G[e] = kNone;
     }
   }
   __syncthreads();
@@ -352,6 +389,9 @@ void launch_seed_transcode(const uint64_t *seed64, SeedEntry32 *seed32, uint64_t
 void launch_seed_extend(const DevIndex &ix, const SeedEntry32 *src, uint32_t d, SeedEntry32 *dst, cudaStream_t st) {
   k_seed_extend<<<grid_for(1ull << (2 * d)), kBlock, 0, st>>>(ix, src, d, dst);
 }
+void launch_seed_pair(const SeedEntry32 *t, uint32_t d, SeedEntryPair *pair, cudaStream_t st) {
+  k_seed_pair<<<grid_for(1ull << (2 * d)), kBlock, 0, st>>>(t, d, pair);
+}
 void launch_count(const DevIndex &ix, const uint8_t *seq, const uint64_t *idx, const uint64_t *len, uint64_t n,
                   bool rc, uint32_t *counts, unsigned long long *counters, cudaStream_t st) {
   if (n == 0) return;
@@ -370,7 +410,8 @@ void launch_free_chain(const DevIndex &ix, const SegParams &P, bool first, cudaS
   k_free_chain<<<grid_for((uint64_t)P.seg_len + 1), kBlock, 0, st>>>(ix, P, first);
 }
 void launch_free_pass1(const DevIndex &ix, const SegParams &P, cudaStream_t st) {
-  k_pass1_tiled<<<grid_for((uint64_t)P.seg_len + 1, kP1Tile), kBlock, 0, st>>>(ix, P);
+  const unsigned g = grid_for((uint64_t)P.seg_len, kP1Tile);
+  k_pass1_tiled<<<g ? g : 1u, kBlock, 0, st>>>(ix, P);
 }
 void launch_free_cert(const DevIndex &ix, const SegParams &P, cudaStream_t st) {
   const uint32_t ngroups = (uint32_t)(((uint64_t)P.seg_len + 1 + P.gsize - 1) / P.gsize);

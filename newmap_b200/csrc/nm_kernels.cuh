@@ -10,6 +10,7 @@ void launch_transcode(const uint8_t *native, uint64_t n_blocks, uint64_t bwt_len
                       uint64_t n64_total, cudaStream_t st);
 void launch_seed_transcode(const uint64_t *seed64, SeedEntry32 *seed32, uint64_t entries, cudaStream_t st);
 void launch_seed_extend(const DevIndex &ix, const SeedEntry32 *src, uint32_t d, SeedEntry32 *dst, cudaStream_t st);
+void launch_seed_pair(const SeedEntry32 *t, uint32_t d, SeedEntryPair *pair, cudaStream_t st);
 void launch_count(const DevIndex &ix, const uint8_t *seq, const uint64_t *idx, const uint64_t *len, uint64_t n,
                   bool rc, uint32_t *counts, unsigned long long *counters, cudaStream_t st);
 void launch_prep(const DevIndex &ix, const SegParams &P, cudaStream_t st);

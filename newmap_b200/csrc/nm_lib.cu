@@ -114,17 +114,32 @@ int set_seed_depth(nm_index *ix, uint32_t depth) {
       return cuda_fail(e, "k_seed_extend");
     }
   }
-  ix->d_seedx = cur;
-  ix->seedx_bytes = (uint64_t)sizeof(nm::SeedEntry32) << (2 * depth);
+  // both strands in one entry: pair[key] = {t[key], t[reverse complement of key]}
+  void *pair = nullptr;
+  const size_t pair_bytes = (size_t)sizeof(nm::SeedEntryPair) << (2 * depth);
+  if (cudaMalloc(&pair, pair_bytes) != cudaSuccess) {
+    cudaGetLastError();
+    cudaFree(cur);
+    return NM_EALLOC;
+  }
+  nm::launch_seed_pair((const nm::SeedEntry32 *)cur, depth, (nm::SeedEntryPair *)pair, 0);
+  const cudaError_t e = cudaDeviceSynchronize();
+  cudaFree(cur);
+  if (e != cudaSuccess) {
+    cudaFree(pair);
+    return cuda_fail(e, "k_seed_pair");
+  }
+  ix->d_seedx = pair;
+  ix->seedx_bytes = pair_bytes;
   ix->device_bytes += ix->seedx_bytes;
-  ix->dev.seedx = (const nm::SeedEntry32 *)cur;
+  ix->dev.seedx = (const nm::SeedEntryPair *)pair;
   ix->dev.seedx_len = depth;
   return NM_OK;
 }
 
 // Depth chosen at load time: the smallest d with 4^d >= 4 * bwtLength (beyond that almost every d-mer of the
 // text is already unique, so a chain is one table lookup plus a step or two), at most 16 (u32 keys), and the
-// table plus its parent level within a third of the free device memory.  NEWMAP_B200_SEED_DEPTH overrides
+// table within what the free device memory allows (see below).  NEWMAP_B200_SEED_DEPTH overrides
 // (0 = none).  Purely a speed matter: results do not depend on it.
 uint32_t auto_seed_depth(const nm_index *ix) {
   if (const char *v = getenv("NEWMAP_B200_SEED_DEPTH")) return (uint32_t)strtoul(v, nullptr, 10);
@@ -132,7 +147,8 @@ uint32_t auto_seed_depth(const nm_index *ix) {
   while (d < 16 && (1ull << (2 * d)) < 4 * ix->dev.bwt_len) ++d;
   size_t free_b = 0, total_b = 0;
   if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) return 0;
-  while (d > ix->dev.seed_len && ((10ull << (2 * d)) > free_b / 3)) --d;  // 8 B x 4^d + 8 B x 4^(d-1)
+  // peak while building: the one-strand table (8 B x 4^d) next to the both-strand one (16 B x 4^d); leave 40 % free
+  while (d > ix->dev.seed_len && ((24ull << (2 * d)) > free_b / 5 * 3)) --d;
   return d;
 }
 
@@ -572,7 +588,8 @@ int nm_workspace_search(nm_workspace *ws, uint64_t num_kmers, int mode, const ui
     const bool deep = dv.seedx && kmin >= dv.seedx_len && ws->opt_ref_lf != 2u;
     P.want_ref_lf = (ws->opt_ref_lf && !deep) ? 1 : 0;
     P.sl = deep ? dv.seedx_len : dv.seed_len;
-    P.seedtab = deep ? dv.seedx : dv.seed32;
+    P.seedtab = deep ? nullptr : dv.seed32;
+    P.seedpair = deep ? dv.seedx : nullptr;
     const uint32_t sl = P.sl;
     P.dcap = ws->opt_dcap ? ws->opt_dcap : (deep ? sl + 8 : sl + 12);
     if (P.dcap <= sl) P.dcap = sl + 1;

@@ -17,7 +17,7 @@ struct EmuIndex {
   std::vector<uint32_t> rank32;
   std::vector<SeedEntry32> seed32;
   std::vector<uint64_t> seed64;
-  std::vector<SeedEntry32> seedx;  // deeper derived table (emu_index_set_seed_depth)
+  std::vector<SeedEntryPair> seedx;  // deeper derived both-strand table (emu_index_set_seed_depth)
   uint32_t c32[8] = {0};
   DevIndex dev{};
   bool has_rank32 = false;
@@ -82,7 +82,8 @@ int emu_index_set_seed_depth(EmuIndex *ix, uint32_t depth) {
     for (uint64_t key = 0; key < (1ull << (2 * d)); ++key) seed_extend_thread(ix->dev, ix->c32, cur.data(), d, next.data(), key);
     cur.swap(next);
   }
-  ix->seedx.swap(cur);
+  ix->seedx.resize((size_t)1 << (2 * depth));
+  for (uint64_t key = 0; key < (1ull << (2 * depth)); ++key) seed_pair_thread(cur.data(), depth, ix->seedx.data(), key);
   ix->dev.seedx = ix->seedx.data();
   ix->dev.seedx_len = depth;
   return 0;
@@ -118,7 +119,8 @@ int emu_min_unique(EmuIndex *ix, const uint8_t *seg, uint32_t seg_len, uint32_t 
   // reference's LF steps is then off, so it is only requested on the index's own table)
   const bool deep = ix->dev.seedx && P.kmin >= ix->dev.seedx_len;
   P.sl = deep ? ix->dev.seedx_len : ix->dev.seed_len;
-  P.seedtab = deep ? ix->dev.seedx : ix->dev.seed32;
+  P.seedtab = deep ? nullptr : ix->dev.seed32;
+  P.seedpair = deep ? ix->dev.seedx : nullptr;
   P.want_ref_lf = deep ? 0 : 1;
   P.dcap = dcap ? dcap : P.sl + 12; if (P.dcap <= P.sl) P.dcap = P.sl + 1;
   for (uint32_t p = 0; p < seg_len; ++p) prep_thread(ix->dev, P, p);

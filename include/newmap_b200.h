@@ -189,6 +189,30 @@ int nm_fasta_read(const nm_fasta *fa, uint64_t seq_offset, uint64_t n, uint8_t *
 /* the workspace's next search reads its segment from the parsed sequence buffer instead of an uploaded one */
 int nm_workspace_attach(nm_workspace *ws, const nm_fasta *fa, uint64_t seq_offset, uint64_t seg_len);
 
+/* ---- `newmap track` on the device (newmap/track.py:22-111): mappability tracks from <id>.unique.uintN ------------
+ * multi-read mappability of position i for read length k = (number of j in (i-k, i] with 0 < unique[j] <= k) / k
+ * (track.py:22-62: +1/-1 interval marks and a cumulative sum); single-read mappability = that number > 0
+ * (track.py:65-68).  The device keeps the integer window counts; the BED runs and the WIG text are produced from
+ * them (run starts by stream compaction; the text by a per-position length scan and a scatter from the k+1
+ * possible strings, which the caller formats once on the host so that the digits are the reference's own). */
+typedef struct nm_track nm_track;
+int nm_track_open(int device, nm_track **out);
+void nm_track_close(nm_track *tr);
+/* uploads n values of width 1/2/4 bytes (host memory) and computes the window counts for read length k */
+int nm_track_compute(nm_track *tr, const void *unique, uint64_t n, int width, uint32_t kmer_length);
+/* window counts (u32) of positions [first, first + m) to host memory */
+int nm_track_counts(nm_track *tr, uint64_t first, uint64_t m, uint32_t *out);
+/* maximal runs of equal single-read value: *nruns = their number; starts/values filled up to capacity (may be NULL) */
+int nm_track_runs(nm_track *tr, uint64_t *starts, uint8_t *values, uint64_t capacity, uint64_t *nruns);
+/* BED lines "<chr>\t<start>\t<end>\tk<k>\t<0|1>\t.\n" (track.py:86-97) of runs [first_run, first_run + m) of the last
+ * nm_track_runs, assembled on the device; *written = bytes produced, NM_EARG if they exceed capacity */
+int nm_track_bed_text(nm_track *tr, const char *chr_name, uint64_t first_run, uint64_t m, char *out, uint64_t capacity,
+                      uint64_t *written);
+/* text of positions [first, first + m): strings[offsets[c] .. offsets[c+1]) + '\n' for the count c of each position
+ * (offsets has kmer_length + 2 entries); *written = bytes produced, NM_EARG if they exceed capacity */
+int nm_track_text(nm_track *tr, const char *strings, const uint32_t *offsets, uint64_t first, uint64_t m, char *out,
+                  uint64_t capacity, uint64_t *written);
+
 /* Pinned host memory for segment / output staging (cudaHostAlloc / cudaFreeHost). */
 void *nm_host_alloc(uint64_t bytes);
 void nm_host_free(void *p);

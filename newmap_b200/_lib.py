@@ -81,6 +81,13 @@ SIGNATURES = {
     "nm_fasta_headers": (_i, [_vp, _vp, _u64, C.POINTER(_u64)]),
     "nm_fasta_read": (_i, [_vp, _u64, _u64, _vp]),
     "nm_workspace_attach": (_i, [_vp, _vp, _u64, _u64]),
+    "nm_track_open": (_i, [_i, C.POINTER(_vp)]),
+    "nm_track_close": (None, [_vp]),
+    "nm_track_compute": (_i, [_vp, _vp, _u64, _i, _u32]),
+    "nm_track_counts": (_i, [_vp, _u64, _u64, _vp]),
+    "nm_track_runs": (_i, [_vp, _vp, _vp, _u64, C.POINTER(_u64)]),
+    "nm_track_bed_text": (_i, [_vp, C.c_char_p, _u64, _u64, _vp, _u64, C.POINTER(_u64)]),
+    "nm_track_text": (_i, [_vp, C.c_char_p, _vp, _u64, _u64, _vp, _u64, C.POINTER(_u64)]),
     "nm_host_alloc": (_vp, [_u64]),
     "nm_host_free": (None, [_vp]),
     "nm_index_build": (_i, [_vp, _u64, _vp, _u64, _vp, _u64, _u32, _u32, _i, C.c_char_p, C.POINTER(C.c_double)]),

@@ -1,11 +1,11 @@
-"""`newmap search` command line, flag-for-flag the reference's (newmap/main.py:89-188), on the
+"""`newmap index | search | track` command line, flag-for-flag the reference's (newmap/main.py:29-251), on the
 B200 path.  `python -m newmap_b200 search genome.fa genome.awfmi -r 20:200 -o out/`."""
 from __future__ import annotations
 
 import sys
 from argparse import ArgumentParser
 
-from . import __version__, index, search
+from . import __version__, index, search, track
 from .util import INDEX_EXTENSION
 
 DEFAULT_KMER_BATCH_SIZE = 10000000
@@ -50,6 +50,19 @@ def build_parser() -> ArgumentParser:
     q.add_argument("--algorithm", choices=["auto", "trajectory", "free_generic"], default="auto",
                    help="auto: trajectory-free kernels (same bytes as the reference); trajectory: replay the "
                         "reference's binary / linear search on the GPU")
+    t = sub.add_parser("track", help="Calculate single and multi-read mappability tracks from shortest unique "
+                                     "sequence lengths (on the GPU)")
+    t.set_defaults(func=track.main)
+    t.add_argument("read_length", nargs="?", default=str(track.DEFAULT_MAPPABILITY_READ_LENGTH), metavar="read_length",
+                   help=f"read length the mappability is calculated for (default {track.DEFAULT_MAPPABILITY_READ_LENGTH})")
+    t.add_argument("unique_count_files", nargs="+", help="one or more unique count files")
+    o = t.add_argument_group("output arguments")
+    o.add_argument("--single-read", "-s", metavar="FILE",
+                   help=f"single-read mappability BED file ('{track.STDOUT_FILENAME}' for standard output; the default "
+                        "when --multi-read is not given)")
+    o.add_argument("--multi-read", "-m", metavar="FILE",
+                   help=f"multi-read mappability WIG file ('{track.STDOUT_FILENAME}' for standard output)")
+    o.add_argument("--verbose", "-v", action="store_true")
     return parser
 
 

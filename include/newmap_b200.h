@@ -82,7 +82,8 @@ typedef struct nm_stats {
   float ms_pass1, ms_cert, ms_pass3;
   uint32_t launches;          /* kernels launched for this call */
   uint32_t seed_depth;        /* depth of the seed table the chains started from */
-  uint32_t reserved;
+  uint32_t short_counts;      /* nm_workspace_multi searches: positions whose summed count fell below the number of
+                                 sequences without being 0 (the reference's range loop never ends there) */
   uint64_t lf_steps_pass1;    /* part of lf_steps executed by the first pass (every position, depth-capped) */
   uint64_t seed_lookups;      /* seed-table lookups of the trajectory-free search */
   uint64_t seed_lookups_pass1;
@@ -148,6 +149,21 @@ int nm_workspace_option(nm_workspace *ws, int option, uint64_t value);
 /* 64-bit FNV-style checksum of the last search's output computed on the device (for
  * device-resident runs that never copy the output back). */
 int nm_workspace_checksum(nm_workspace *ws, uint64_t *sum);
+
+/* ---- several sequences x several indexes at once ----------------------------------------------
+ * Replaces newmap/search.py:260-265 (zip of the n-th segments of every FASTA file), :461,:489-517 (range mode) /
+ * :575,:627-639 (list mode) and :656-697 (get_kmer_counts): the count of a (position, length) is the sum over
+ * every index and every sequence, both strands unless use_rc == 0, and a length is unique when the sum equals the
+ * number of sequences.  Call after nm_workspace_upload (which carries the segment of the FIRST file: start mask,
+ * barriers and length limits come from it alone, search.py:391-394) and before nm_workspace_search:
+ *   indexes   n_indexes (1..8) open indexes on the workspace's device, in the order of --index-file;
+ *   segments  n_segments (0..7) HOST buffers, the same segment of the 2nd, 3rd ... FASTA file, each of the uploaded
+ *             segment's length (the reference assumes equal lengths, search.py:391).
+ * The following nm_workspace_search runs on the reference's own query trajectory whatever `algo` says.  The setting
+ * lasts until the next nm_workspace_upload / nm_workspace_attach.  nm_stats.short_counts > 0 after the search means
+ * the reference would not have terminated (a sum below the number of sequences that is not 0). */
+int nm_workspace_multi(nm_workspace *ws, nm_index *const *indexes, uint32_t n_indexes, const uint8_t *const *segments,
+                       uint32_t n_segments);
 
 /* ---- FASTA ingest on the device (replaces newmap/fasta.py:20-190 sequence_segments for the plain-text case) ------
  * The raw text of a FASTA file is copied to the GPU as it is read (pinned staging, several reader threads), and

@@ -33,7 +33,7 @@ class Stats(C.Structure):
                 ("replayed", C.c_uint32), ("ms_h2d", C.c_float), ("ms_prep", C.c_float), ("ms_search", C.c_float),
                 ("ms_generic", C.c_float), ("ms_resolve", C.c_float), ("ms_d2h", C.c_float), ("ms_total", C.c_float),
                 ("ms_pass1", C.c_float), ("ms_cert", C.c_float), ("ms_pass3", C.c_float), ("launches", C.c_uint32),
-                ("seed_depth", C.c_uint32), ("reserved", C.c_uint32), ("lf_steps_pass1", C.c_uint64),
+                ("seed_depth", C.c_uint32), ("short_counts", C.c_uint32), ("lf_steps_pass1", C.c_uint64),
                 ("seed_lookups", C.c_uint64), ("seed_lookups_pass1", C.c_uint64)]
 
     def as_dict(self) -> dict:
@@ -80,6 +80,7 @@ SIGNATURES = {
     "nm_fasta_records": (_i, [_vp, C.POINTER(FastaRecord), _u64]),
     "nm_fasta_headers": (_i, [_vp, _vp, _u64, C.POINTER(_u64)]),
     "nm_fasta_read": (_i, [_vp, _u64, _u64, _vp]),
+    "nm_workspace_multi": (_i, [_vp, C.POINTER(_vp), C.c_uint32, C.POINTER(_vp), C.c_uint32]),
     "nm_workspace_attach": (_i, [_vp, _vp, _u64, _u64]),
     "nm_track_open": (_i, [_i, C.POINTER(_vp)]),
     "nm_track_close": (None, [_vp]),
@@ -160,12 +161,23 @@ class Index:
     """A reference-built .awfmi resident in the HBM of one GPU (opened once, not once per call
     like newmap-count.c:9-17,136)."""
 
-    def __init__(self, path, device: int | None = None):
+    def __init__(self, path, device: int | None = None, seed_depth: int | None = None):
+        """seed_depth: depth of the derived seed table (None = chosen by the library, 0 = none)."""
         L = load()
         if device is None:
             device = int(os.environ.get("NEWMAP_B200_DEVICE", os.environ.get("LOCAL_RANK", "0")))
         h = _vp()
-        check(L.nm_index_open(os.fsencode(str(path)), device, C.byref(h)), f"nm_index_open({path})")
+        old = os.environ.get("NEWMAP_B200_SEED_DEPTH")
+        if seed_depth is not None:
+            os.environ["NEWMAP_B200_SEED_DEPTH"] = str(int(seed_depth))
+        try:
+            check(L.nm_index_open(os.fsencode(str(path)), device, C.byref(h)), f"nm_index_open({path})")
+        finally:
+            if seed_depth is not None:
+                if old is None:
+                    os.environ.pop("NEWMAP_B200_SEED_DEPTH", None)
+                else:
+                    os.environ["NEWMAP_B200_SEED_DEPTH"] = old
         self._h = h
         self.path = str(path)
         self.device = device
@@ -289,6 +301,16 @@ class Workspace:
 
     def upload(self, seg_ptr: int, seg_len: int):
         check(load().nm_workspace_upload(self._h, seg_ptr, int(seg_len)), "nm_workspace_upload")
+
+    def multi(self, indexes: list, segment_ptrs: list):
+        """Several sequences x several indexes (search.py:461,656-697): the next search sums the counts over `indexes`
+        and over the uploaded segment plus the host buffers `segment_ptrs` (same length, one per further FASTA)."""
+        ih = (_vp * len(indexes))(*[ix._h for ix in indexes])
+        sp = (_vp * max(len(segment_ptrs), 1))(*[_vp(p) for p in segment_ptrs])
+        rc = load().nm_workspace_multi(self._h, ih, len(indexes), sp, len(segment_ptrs))
+        if rc == NM_EARG:
+            raise ValueError("between 1 and 8 indexes on the workspace's device and at most 7 further sequences")
+        check(rc, "nm_workspace_multi")
 
     def search(self, num_kmers: int, kmer_lengths, is_range: bool, initial_search_length: int = 0,
                use_rc: bool = True, algo: str = "auto", out_width: int = 1):

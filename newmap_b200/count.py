@@ -13,8 +13,8 @@ _cache: dict = {}
 _cache_lock = threading.Lock()
 
 
-def open_index(index_path, device: int | None = None) -> _lib.Index:
-    """Process-wide cache of resident indexes keyed by (real path, mtime, size, device)."""
+def open_index(index_path, device: int | None = None, seed_depth: int | None = None) -> _lib.Index:
+    """Process-wide cache of resident indexes keyed by (real path, mtime, size, device, derived seed depth asked for)."""
     if device is None:
         device = int(os.environ.get("NEWMAP_B200_DEVICE", os.environ.get("LOCAL_RANK", "0")))
     path = os.path.realpath(os.fspath(index_path))
@@ -22,11 +22,11 @@ def open_index(index_path, device: int | None = None) -> _lib.Index:
         st = os.stat(path)
     except OSError:
         raise OSError("Could not load reference index from file\n")     # newmap-count.c:13-16
-    key = (path, st.st_mtime_ns, st.st_size, device)
+    key = (path, st.st_mtime_ns, st.st_size, device, seed_depth)
     with _cache_lock:
         ix = _cache.get(key)
         if ix is None or ix._h is None:
-            ix = _lib.Index(path, device)
+            ix = _lib.Index(path, device, seed_depth)
             _cache[key] = ix
         return ix
 

@@ -116,6 +116,7 @@ enum { CTR_LF = 0, CTR_QUERIES = 1, CTR_GENERIC = 2, CTR_ANOMALY = 3, CTR_ZERO_K
        CTR_LF_PASS1 = 6,  // LF steps of the first (depth-capped, every position) pass of the trajectory-free search
        CTR_SEEDS = 7,     // seed-table lookups of the trajectory-free search (one 32-byte sector each)
        CTR_SEEDS_PASS1 = 8,  // the part of CTR_SEEDS looked up by the first pass
+       CTR_SHORT = 9,     // multi search: positions whose summed count fell below the number of sequences (not 0)
        CTR_N = 16 };
 
 struct alignas(8) SeedEntry32 {  // one 64-bit load
@@ -433,6 +434,76 @@ NM_HD void trajectory_thread(const DevIndex &ix, const SegParams &P, uint32_t i,
         ++nq;
         if (c == 0) { note_zero(P, j, i, cut); break; }
         if (c == 1) { best = k; break; }        // :627-639 (nominal k recorded)
+      }
+    }
+  }
+  store_out(P, i, best);
+}
+
+// ---------------------------------------------------------------------------------------------
+// (M) several sequences x several indexes at once (search.py:461,489-517 range mode, :575,:627-639 list mode,
+// :656-697 the count): the count of a (position, length) is summed over every index and every sequence, both strands
+// unless --norc, in uint32; a length is unique when the sum equals the number of SEQUENCES.  Start mask, barriers and
+// length limits come from the first sequence only (search.py:391-394, :557-560).  One position per thread on the
+// reference's own query trajectory.  A sum below the number of sequences that is not 0 matches no rule of the
+// reference's range loop (it would repeat the same query for ever): the position is left at what it has found and
+// counted in CTR_SHORT for the caller to refuse.
+// ---------------------------------------------------------------------------------------------
+constexpr uint32_t kMaxMulti = 8;
+struct MultiSet {
+  DevIndex ix[kMaxMulti];
+  const uint8_t *seg[kMaxMulti];  // seg[0] == P.seg; all of P.seg_len bytes
+  uint32_t n_ix, n_seq;
+};
+
+NM_HD uint32_t count_multi(const MultiSet &M, uint64_t i, uint64_t k, bool use_rc, uint32_t &steps) {
+  uint32_t c = 0;
+  for (uint32_t x = 0; x < M.n_ix; ++x)
+    for (uint32_t s = 0; s < M.n_seq; ++s) c += count_both(M.ix[x], M.seg[s], i, k, use_rc, steps);
+  return c;
+}
+
+NM_HD void trajectory_multi_thread(const MultiSet &M, const SegParams &P, uint32_t i, uint32_t &steps, uint32_t &nq,
+                                   uint32_t &nshort) {
+  uint32_t best = 0;
+  const uint32_t S = M.n_seq;
+  const uint8_t ch = ld8(P.seg + i);
+  if (start_allowed(ch)) {
+    if (P.mode == 0) {
+      const uint32_t ub = length_limit(P, i);
+      if (ub >= P.kmin) {
+        uint32_t lo = P.kmin, hi = ub;
+        uint32_t q = (lo + hi) / 2;
+        if (P.initial && q > P.initial) q = P.initial;
+        for (uint32_t round = 0;; ++round) {
+          const uint32_t c = count_multi(M, i, q, P.use_rc != 0, steps);
+          ++nq;
+          if (c == 0) { note_zero(P, round, i, q); break; }
+          if (c == S) {                         // search.py:489-508, :524-527
+            if (best == 0 || q < best) best = q;
+            if (q == lo) break;
+            hi = q - 1;
+          } else if (c > S) {                   // :513-517, :532-535
+            if (q == hi) break;
+            lo = q + 1;
+          } else {
+            ++nshort;
+            break;
+          }
+          q = (lo + hi) / 2;
+        }
+      }
+    } else {
+      const uint32_t b = next_barrier(P, i);
+      for (uint32_t j = 0; j < P.nk; ++j) {
+        const uint32_t k = P.klist[j];
+        const uint32_t cut = (k <= P.seg_len - i) ? k : P.seg_len - i;
+        if (b != kNoBarrier && b - i < cut) break;
+        const uint32_t c = count_multi(M, i, cut, P.use_rc != 0, steps);
+        ++nq;
+        if (c == 0) { note_zero(P, j, i, cut); break; }
+        if (c == S && best == 0) best = k;      // :627-636: first length whose sum equals the number of sequences
+        if (c == 1) break;                      // :639: only a sum of exactly 1 retires the position
       }
     }
   }

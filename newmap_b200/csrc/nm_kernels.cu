@@ -152,6 +152,15 @@ __global__ void __launch_bounds__(kBlock) k_trajectory(DevIndex ix, SegParams P)
   flush_counter(&P.counters[CTR_QUERIES], nq);
 }
 
+__global__ void __launch_bounds__(kBlock) k_trajectory_multi(const MultiSet *M, SegParams P) {
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  uint32_t steps = 0, nq = 0, nshort = 0;
+  if (i < P.num_kmers) trajectory_multi_thread(*M, P, i, steps, nq, nshort);
+  flush_counter(&P.counters[CTR_LF], steps);
+  flush_counter(&P.counters[CTR_QUERIES], nq);
+  flush_counter(&P.counters[CTR_SHORT], nshort);
+}
+
 // prefix sums as u32[6] staged in shared memory (dynamic indexing of kernel parameters would spill to local memory)
 __device__ __forceinline__ const uint32_t *stage_c32(const DevIndex &ix, uint32_t *sC) {
   if (threadIdx.x < 6) sC[threadIdx.x] = ix.c32[threadIdx.x];
@@ -405,6 +414,10 @@ void launch_prep(const DevIndex &ix, const SegParams &P, cudaStream_t st) {
 void launch_trajectory(const DevIndex &ix, const SegParams &P, cudaStream_t st) {
   if (P.num_kmers == 0) return;
   k_trajectory<<<grid_for(P.num_kmers), kBlock, 0, st>>>(ix, P);
+}
+void launch_trajectory_multi(const MultiSet *M, const SegParams &P, cudaStream_t st) {
+  if (P.num_kmers == 0) return;
+  k_trajectory_multi<<<grid_for(P.num_kmers), kBlock, 0, st>>>(M, P);
 }
 void launch_free_chain(const DevIndex &ix, const SegParams &P, bool first, cudaStream_t st) {
   k_free_chain<<<grid_for((uint64_t)P.seg_len + 1), kBlock, 0, st>>>(ix, P, first);

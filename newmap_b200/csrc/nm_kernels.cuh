@@ -15,6 +15,7 @@ void launch_count(const DevIndex &ix, const uint8_t *seq, const uint64_t *idx, c
                   bool rc, uint32_t *counts, unsigned long long *counters, cudaStream_t st);
 void launch_prep(const DevIndex &ix, const SegParams &P, cudaStream_t st);
 void launch_trajectory(const DevIndex &ix, const SegParams &P, cudaStream_t st);
+void launch_trajectory_multi(const MultiSet *M, const SegParams &P, cudaStream_t st);
 void launch_free_chain(const DevIndex &ix, const SegParams &P, bool first, cudaStream_t st);  // pass 1 / pass 3
 void launch_free_pass1(const DevIndex &ix, const SegParams &P, cudaStream_t st);                 // pass 1, tiled kernel
 void launch_free_cert(const DevIndex &ix, const SegParams &P, cudaStream_t st);               // pass 2

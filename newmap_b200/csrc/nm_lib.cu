@@ -5,6 +5,7 @@
 
 #include <cstdio>
 #include <cstdlib>
+#include <algorithm>
 #include <cstring>
 #include <mutex>
 #include <new>
@@ -71,6 +72,10 @@ struct nm_workspace {
   bool timed_h2d = false, timed_d2h = false;
   void *pending_out = nullptr;
   uint32_t opt_ref_lf = 0, opt_dcap = 0, opt_gsize = 0, opt_pass1 = 0;
+  // several sequences x several indexes (nm_workspace_multi); cleared by the next upload / attach
+  nm::MultiSet *d_multi = nullptr;
+  uint8_t *d_extra[nm::kMaxMulti]{};  // extra sequences' segments, max_seg_len + 16 bytes each, allocated on demand
+  uint32_t multi_ix = 0, multi_seq = 0;
 };
 
 namespace {
@@ -293,7 +298,8 @@ int run_search(nm_workspace *ws, int algo) {
   ws->launches = P.seg_len ? 1u : 0u;
   NM_CUDA(cudaEventRecord(ws->ev[EV_PREP1], st));
   if (algo == NM_ALGO_TRAJECTORY) {
-    nm::launch_trajectory(ix->dev, P, st);
+    if (ws->multi_ix) nm::launch_trajectory_multi(ws->d_multi, P, st);
+    else nm::launch_trajectory(ix->dev, P, st);
     ws->launches += P.num_kmers ? 1u : 0u;
     NM_CUDA(cudaEventRecord(ws->ev[EV_PASS1], st));
     NM_CUDA(cudaEventRecord(ws->ev[EV_CERT1], st));
@@ -485,6 +491,8 @@ void nm_workspace_destroy(nm_workspace *ws) {
   cudaFree(ws->d_R);
   cudaFree(ws->d_out);
   cudaFree(ws->d_klist);
+  cudaFree(ws->d_multi);
+  for (auto *p : ws->d_extra) cudaFree(p);
   cudaFree(ws->d_counters);
   if (ws->h_counters) cudaFreeHost(ws->h_counters);
   for (auto &e : ws->ev)
@@ -502,6 +510,40 @@ int nm_workspace_upload(nm_workspace *ws, const uint8_t *seg, uint64_t seg_len) 
   ws->seg_ext = nullptr;
   ws->timed_h2d = true;
   ws->have_search = false;
+  ws->multi_ix = ws->multi_seq = 0;
+  return NM_OK;
+}
+
+int nm_workspace_multi(nm_workspace *ws, nm_index *const *indexes, uint32_t n_indexes, const uint8_t *const *segments,
+                       uint32_t n_segments) {
+  if (!ws || !indexes || n_indexes == 0 || n_indexes > nm::kMaxMulti || n_segments + 1 > nm::kMaxMulti ||
+      (n_segments && !segments) || ws->seg_ext)
+    return NM_EARG;
+  for (uint32_t x = 0; x < n_indexes; ++x)
+    if (!indexes[x] || indexes[x]->device != ws->ix->device) return NM_EARG;
+  for (uint32_t j = 0; j < n_segments; ++j)
+    if (!segments[j] && ws->seg_len) return NM_EARG;
+  NM_CUDA(cudaSetDevice(ws->ix->device));
+  if (!ws->d_multi) NM_CUDA(cudaMalloc((void **)&ws->d_multi, sizeof(nm::MultiSet)));
+  nm::MultiSet M;
+  memset(&M, 0, sizeof M);
+  M.n_ix = n_indexes;
+  M.n_seq = n_segments + 1;
+  for (uint32_t x = 0; x < n_indexes; ++x) M.ix[x] = indexes[x]->dev;
+  M.seg[0] = ws->d_seg;
+  for (uint32_t j = 0; j < n_segments; ++j) {
+    if (!ws->d_extra[j]) NM_CUDA(cudaMalloc((void **)&ws->d_extra[j], ws->max_seg_len + 16));
+    if (ws->seg_len)
+      NM_CUDA(cudaMemcpyAsync(ws->d_extra[j], segments[j], ws->seg_len, cudaMemcpyHostToDevice, ws->stream));
+    M.seg[j + 1] = ws->d_extra[j];
+  }
+  // the set is read by the kernel of the search that follows on the same stream; the copy source is this stack
+  // frame, so the copy is synchronous with respect to the host
+  NM_CUDA(cudaMemcpyAsync(ws->d_multi, &M, sizeof M, cudaMemcpyHostToDevice, ws->stream));
+  NM_CUDA(cudaStreamSynchronize(ws->stream));
+  ws->multi_ix = n_indexes;
+  ws->multi_seq = n_segments + 1;
+  ws->have_search = false;
   return NM_OK;
 }
 
@@ -515,6 +557,7 @@ int nm_workspace_attach(nm_workspace *ws, const nm_fasta *fa, uint64_t seq_offse
   NM_CUDA(cudaSetDevice(ws->ix->device));
   NM_CUDA(cudaEventRecord(ws->ev[EV_H2D0], ws->stream));
   ws->seg_ext = seq + seq_offset;
+  ws->multi_ix = ws->multi_seq = 0;
   ws->seg_len = seg_len;
   ws->timed_h2d = true;
   ws->have_search = false;
@@ -595,6 +638,7 @@ int nm_workspace_search(nm_workspace *ws, uint64_t num_kmers, int mode, const ui
     if (P.dcap <= sl) P.dcap = sl + 1;
     P.gsize = ws->opt_gsize ? ws->opt_gsize : 16;
   }
+  if (ws->multi_ix) algo = NM_ALGO_TRAJECTORY;  // the summed count is searched on the reference's own trajectory
   ws->algo_req = algo;
   ws->have_search = true;
   ws->timed_d2h = false;
@@ -661,6 +705,7 @@ int nm_workspace_sync(nm_workspace *ws, nm_stats *stats) {
     stats->seed_lookups_pass1 = seeds_pass1;
     stats->launches = ws->launches + (replayed ? free_launches : 0u);
     stats->seed_depth = ws->P.sl;
+    stats->short_counts = (uint32_t)std::min<unsigned long long>(ws->h_counters[nm::CTR_SHORT], 0xFFFFFFFFull);
     stats->ms_pass1 = ms[7];
     stats->ms_cert = ms[8];
     stats->ms_pass3 = ms[9];

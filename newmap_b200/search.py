@@ -160,43 +160,96 @@ def _raise_zero_count(segment_data: bytes, st: _lib.Stats):
                        f"Possibly a mismatch between the sequence and the index.")
 
 
-def _single(config: SearchConfig):
-    if len(config.fmindex_filepaths) != 1:
-        raise NotImplementedError("newmap_b200: simultaneous search over several index files is not built yet "
-                                  "(SURVEY.md §8(f) N3)")
-    return open_index(config.fmindex_filepaths[0], config.device)
+def _is_multi(config: SearchConfig) -> bool:
+    return len(config.fasta_filepaths) > 1 or len(config.fmindex_filepaths) > 1
 
 
 def get_kmer_counts(config: SearchConfig, sequences: list, sequence_indices: list, kmer_lengths: list) -> np.ndarray:
-    """Two-strand u32 counts of sequences[0][i:i+k] (search.py:647-724) on the GPU."""
-    if len(sequences) != 1:
-        raise NotImplementedError("newmap_b200: one sequence per call (SURVEY.md §8(f) N3)")
-    ix = _single(config)
-    seq = sequences[0]
-    total = ix.count(seq, sequence_indices, kmer_lengths)
-    if config.use_reverse_complement:
-        total = total + ix.count(seq, sequence_indices, kmer_lengths, reverse_complement=True)
+    """u32 counts of sequences[*][i:i+k] summed over every index, every sequence and both strands
+    (search.py:647-724) on the GPU."""
+    total = np.zeros(len(sequence_indices), dtype=np.uint32)
+    for fmindex_filepath in config.fmindex_filepaths:
+        ix = open_index(fmindex_filepath, config.device)
+        for i, seq in enumerate(sequences):
+            if len(sequences) > 1:
+                # search.py:664-668 names the i-th INDEX file for the i-th sequence: IndexError with fewer indexes
+                config.log(f"Counting k-mers from {config.fmindex_filepaths[i]} in index {fmindex_filepath}")
+            total += ix.count(seq, sequence_indices, kmer_lengths)
+            if config.use_reverse_complement:
+                total += ix.count(seq, sequence_indices, kmer_lengths, reverse_complement=True)
     zero = np.nonzero(total == 0)[0]
     if zero.size:
         i, k = sequence_indices[int(zero[0])], kmer_lengths[int(zero[0])]
         raise RuntimeError(f"The following generated k-mer was not found in the index:\n"
-                           f"{bytes(seq[i:i + k]).decode('utf-8')}\n"
+                           f"{bytes(sequences[0][i:i + k]).decode('utf-8')}\n"
                            f"Possibly a mismatch between the sequence and the index.")
     return total
 
 
+class _MultiSearcher:
+    """Several FASTA files x several index files (search.py:260-265,461,489-517,656-697): one
+    workspace, every index resident on the same GPU without derived tables (the summed count is searched on the
+    reference's own query trajectory, nm_workspace_multi)."""
+
+    def __init__(self, config: SearchConfig, max_seg_len: int):
+        self.config = config
+        self.indexes = [open_index(p, config.device, seed_depth=0) for p in config.fmindex_filepaths]
+        self.ws = _lib.Workspace(self.indexes[0], max_seg_len)
+        self.max_seg_len = max_seg_len
+
+    def close(self):
+        self.ws.close()
+
+    def search(self, sequence_segments_: tuple, num_kmers: int, data_type) -> np.ndarray:
+        config = self.config
+        first = sequence_segments_[0]
+        n = len(first.data)
+        datas = [_lib.as_u8(s.data) for s in sequence_segments_]
+        for d in datas[1:]:
+            if d.size != n:
+                raise ValueError("the sequences of the FASTA files given together must be equal in length "
+                                 "(search.py:391-392)")
+        if len(sequence_segments_) > len(self.indexes) and num_kmers and \
+                not get_ambiguous_sequence_mask(first, num_kmers).all():
+            # search.py:664-668 (see get_kmer_counts): the reference stops here with this error
+            raise IndexError("list index out of range")
+        if n > self.max_seg_len:
+            self.ws.close()
+            self.ws = _lib.Workspace(self.indexes[0], n)
+            self.max_seg_len = n
+        out = np.zeros(max(num_kmers, 1), dtype=data_type)
+        self.ws.upload(datas[0].ctypes.data, n)
+        self.ws.multi(self.indexes, [d.ctypes.data for d in datas[1:]])
+        self.ws.search(num_kmers, config.kmer_lengths, config.is_binary_search, config.initial_search_length,
+                       config.use_reverse_complement, "trajectory", np.dtype(data_type).itemsize)
+        self.ws.download(out.ctypes.data)
+        st = self.ws.sync()
+        if st.zero_pos >= 0:
+            _raise_zero_count(first.data, st)
+        if st.short_counts:
+            raise RuntimeError(f"{st.short_counts} position(s) had a total count below the number of sequences "
+                               f"({len(sequence_segments_)}): the sequences do not all occur in the indexes given "
+                               "(the reference does not terminate on such input)")
+        return out[:num_kmers]
+
+
 def _search_segment(config: SearchConfig, sequence_segments_: tuple, data_type) -> tuple:
-    if len(sequence_segments_) != 1:
-        raise NotImplementedError("newmap_b200: one FASTA per search (SURVEY.md §8(f) N3)")
     seg = sequence_segments_[0]
     max_k = max(config.kmer_lengths)
     num_kmers = get_num_kmers(seg, max_k)
-    ix = _single(config)
-    out, st = ix.min_unique(seg.data, num_kmers, config.kmer_lengths, config.is_binary_search,
-                            config.initial_search_length, config.use_reverse_complement, config.algorithm,
-                            dtype=data_type)
-    if st.zero_pos >= 0:
-        _raise_zero_count(seg.data, st)
+    if len(sequence_segments_) > 1 or len(config.fmindex_filepaths) > 1:
+        ms = _MultiSearcher(config, len(seg.data))
+        try:
+            out = ms.search(tuple(sequence_segments_), num_kmers, data_type)
+        finally:
+            ms.close()
+    else:
+        ix = open_index(config.fmindex_filepaths[0], config.device)
+        out, st = ix.min_unique(seg.data, num_kmers, config.kmer_lengths, config.is_binary_search,
+                                config.initial_search_length, config.use_reverse_complement, config.algorithm,
+                                dtype=data_type)
+        if st.zero_pos >= 0:
+            _raise_zero_count(seg.data, st)
     ambiguous = int(get_ambiguous_sequence_mask(seg, num_kmers).sum())
     return out, ambiguous
 
@@ -236,13 +289,12 @@ def write_unique_counts(config: SearchConfig):
     max_kmer_length = max(config.kmer_lengths)
     min_kmer_length = min(config.kmer_lengths)
     data_type, unique_count_suffix = _lib.out_dtype(max_kmer_length)
-    if len(config.fasta_filepaths) != 1 or len(config.fmindex_filepaths) != 1:
-        raise NotImplementedError("newmap_b200: simultaneous search over several FASTA / index files is not "
-                                  "built yet (SURVEY.md §8(f) N3)")
     if config.is_binary_search and max_kmer_length > min_kmer_length:
         config.log("Max {} iterations over range {}-{}".format(
             ceil(log2(max_kmer_length - min_kmer_length) + 1), min_kmer_length, max_kmer_length))
 
+    if _is_multi(config):
+        return _write_unique_counts_multi(config, data_type, unique_count_suffix)
     ix = open_index(config.fmindex_filepaths[0], config.device)
     lookahead_length = max_kmer_length - 1
     requested_sequence_length = config.kmer_batch_size + lookahead_length
@@ -339,6 +391,80 @@ def write_unique_counts(config: SearchConfig):
             slot.ws.download(slot.out.ptr)
             inflight.append(slot)
         drain()
+        print_summary_statisitcs(config, current_sequence_id, totals["unique"], totals["ambiguous"],
+                                 totals["none"], totals["max_len"], totals["min_len"])
+    if not sequence_processed:
+        if config.include_sequence_ids:
+            raise ValueError(f"None of the included sequences were found: {config.include_sequence_ids}")
+        elif config.exclude_sequence_ids:
+            raise ValueError("The excluded sequences were too strict and nothing was processed: "
+                             f"{config.exclude_sequence_ids}")
+
+
+def _write_unique_counts_multi(config: SearchConfig, data_type, unique_count_suffix: str):
+    """write_unique_counts for several FASTA and / or index files (search.py:222-357 with zip(*sequences)): the n-th
+    segments of every file are searched together; ids, filters and output files follow the first file."""
+    max_kmer_length = max(config.kmer_lengths)
+    min_kmer_length = min(config.kmer_lengths)
+    lookahead_length = max_kmer_length - 1
+    requested_sequence_length = config.kmer_batch_size + lookahead_length
+    if not 0 <= config.rank < config.world_size:
+        raise ValueError("rank must be in [0, world_size)")
+    sharded = config.world_size > 1
+    totals = dict(ambiguous=0, unique=0, none=0, max_len=min_kmer_length, min_len=max_kmer_length)
+    sequence_processed = False
+    current_sequence_id = b""
+    current_file = None
+    segment_number = -1
+    segment_in_sequence = 0
+    searcher = _MultiSearcher(config, requested_sequence_length)
+    with ExitStack() as stack:
+        stack.callback(searcher.close)
+        fasta_files = [stack.enter_context(optional_gzip_open(f, "rb")) for f in config.fasta_filepaths]
+        sequences = [sequence_segments(f, requested_sequence_length, lookahead_length) for f in fasta_files]
+        for segment_list in zip(*sequences):
+            segment = segment_list[0]
+            if current_sequence_id != segment.id:
+                if config.include_sequence_ids or config.exclude_sequence_ids:
+                    if (segment.id not in config.include_sequence_ids) or (segment.id in config.exclude_sequence_ids):
+                        continue
+                sequence_processed = True
+                print_summary_statisitcs(config, current_sequence_id, totals["unique"], totals["ambiguous"],
+                                         totals["none"], totals["max_len"], totals["min_len"])
+                current_sequence_id = segment.id
+                path = config.output_directory / UNIQUE_COUNT_FILENAME_FORMAT.format(
+                    segment.id.decode(), unique_count_suffix)
+                if current_file is not None:
+                    current_file.close()
+                if sharded:
+                    fd = os.open(path, os.O_RDWR | os.O_CREAT, 0o644)
+                    current_file = stack.enter_context(os.fdopen(fd, "r+b"))
+                else:
+                    current_file = stack.enter_context(open(path, "wb"))
+                segment_in_sequence = 0
+                config.log("Writing unique lengths for sequence ID: {}".format(segment.id.decode()))
+            num_kmers = get_num_kmers(segment, max_kmer_length)
+            segment_number += 1
+            offset = segment_in_sequence * config.kmer_batch_size
+            segment_in_sequence += 1
+            if segment_number % config.world_size != config.rank:
+                continue
+            config.log("Processing {} k-mers".format(num_kmers))
+            res = searcher.search(segment_list, num_kmers, data_type)
+            if config.verbose:
+                ambiguous = int(get_ambiguous_sequence_mask(segment, num_kmers).sum())
+                unique = int(np.count_nonzero(res))
+                totals["ambiguous"] += ambiguous
+                totals["unique"] += unique
+                totals["none"] += num_kmers - unique - ambiguous
+                if unique:
+                    totals["max_len"] = max(totals["max_len"], int(res.max()))
+                    totals["min_len"] = min(totals["min_len"], int(res[res != 0].min()))
+                else:
+                    config.log("No unique lengths found for this sequence segment")
+            os.pwrite(current_file.fileno(), res.tobytes(), offset * data_type.itemsize)
+            if segment.epilogue:
+                os.ftruncate(current_file.fileno(), (offset + num_kmers) * data_type.itemsize)
         print_summary_statisitcs(config, current_sequence_id, totals["unique"], totals["ambiguous"],
                                  totals["none"], totals["max_len"], totals["min_len"])
     if not sequence_processed:

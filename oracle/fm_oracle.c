@@ -387,3 +387,86 @@ int ora_min_unique_list(const ora_index *ix, const uint8_t *seg, uint64_t seg_le
   if (queries) *queries += queries_all;
   return 0;
 }
+
+/* Several sequences x several indexes (search.py:461,489-517 range; :575,:627-639 list; :656-697 the count):
+ * the count of a (position, length) is the uint32 sum over every index and every sequence of both_strands(); a
+ * length is unique when the sum equals the number of SEQUENCES.  Start mask, 'N' rule and upper bounds come from
+ * segs[0] only (:391-394, :557-560).  A sum in (0, n_seq) matches neither rule of the range loop (:489-535): the
+ * reference would repeat the query for ever; reported as return code 1 (outputs for other positions are valid). */
+static uint32_t multi_count(const ora_index *const *ixs, uint32_t n_ix, const uint8_t *const *segs, uint32_t n_seq,
+                            uint64_t seg_len, uint64_t i, uint64_t k, int use_rc, uint64_t *steps) {
+  uint32_t c = 0;
+  for (uint32_t x = 0; x < n_ix; ++x)
+    for (uint32_t s = 0; s < n_seq; ++s) c += both_strands(ixs[x], segs[s], seg_len, i, k, use_rc, steps);
+  return c;
+}
+
+int ora_min_unique_multi(const ora_index *const *ixs, uint32_t n_ix, const uint8_t *const *segs, uint32_t n_seq,
+                         uint64_t seg_len, uint64_t num_kmers, int range_mode, const uint32_t *klist, uint32_t nk,
+                         uint32_t initial_len, int use_rc, uint32_t *out, int64_t zero_info[3], uint64_t *lf_steps,
+                         uint64_t *queries) {
+  if (n_ix == 0 || n_seq == 0 || nk == 0 || num_kmers > seg_len) return -1;
+  const uint8_t *seg = segs[0];
+  uint32_t min_k = klist[0], max_k = klist[0];
+  for (uint32_t j = 0; j < nk; ++j) {
+    if (klist[j] == 0) return -1;
+    if (klist[j] < min_k) min_k = klist[j];
+    if (klist[j] > max_k) max_k = klist[j];
+  }
+  if (range_mode && initial_len && initial_len < min_k) return -1;
+  uint8_t *mask = calloc(num_kmers ? num_kmers : 1, 1);
+  uint32_t *ub = malloc((num_kmers ? num_kmers : 1) * sizeof *ub);
+  if (!mask || !ub) { free(mask); free(ub); return -4; }
+  for (uint64_t i = 0; i < num_kmers; ++i) mask[i] = !start_allowed(seg[i]);
+  if (range_mode) ora_upper_bounds(mask, num_kmers, seg_len, max_k, ub);
+  zero_event z = {0, 0, 0, 0};
+  uint64_t steps = 0, nq = 0;
+  int shorted = 0;
+  for (uint64_t i = 0; i < num_kmers; ++i) {
+    out[i] = 0;
+    if (mask[i]) continue;
+    uint32_t best = 0;
+    if (range_mode) {
+      if (ub[i] < min_k) continue;
+      uint32_t lo = min_k, hi = ub[i];
+      uint32_t q = (lo + hi) / 2;
+      if (initial_len && q > initial_len) q = initial_len;
+      for (uint64_t round = 0;; ++round) {
+        const uint32_t c = multi_count(ixs, n_ix, segs, n_seq, seg_len, i, q, use_rc, &steps);
+        ++nq;
+        if (c == 0) { note_zero(&z, round, i, q); break; }
+        if (c == n_seq) {
+          if (best == 0 || q < best) best = q;
+          if (q == lo) break;
+          hi = q - 1;
+        } else if (c > n_seq) {
+          if (q == hi) break;
+          lo = q + 1;
+        } else { shorted = 1; break; }
+        q = (lo + hi) / 2;
+      }
+    } else {
+      for (uint32_t j = 0; j < nk; ++j) {
+        const uint64_t k = klist[j];
+        const uint64_t cut = (i + k <= seg_len) ? k : seg_len - i;
+        if (memchr(seg + i, 'N', cut)) break;
+        const uint32_t c = multi_count(ixs, n_ix, segs, n_seq, seg_len, i, cut, use_rc, &steps);
+        ++nq;
+        if (c == 0) { note_zero(&z, j, i, cut); break; }
+        if (c == n_seq && best == 0) best = (uint32_t)k; /* :627-636 */
+        if (c == 1) break;                               /* :639 */
+      }
+    }
+    out[i] = best;
+  }
+  if (zero_info) {
+    zero_info[0] = z.seen ? (int64_t)z.pos : -1;
+    zero_info[1] = (int64_t)z.len;
+    zero_info[2] = (int64_t)z.round;
+  }
+  if (lf_steps) *lf_steps += steps;
+  if (queries) *queries += nq;
+  free(mask);
+  free(ub);
+  return shorted;
+}

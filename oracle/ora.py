@@ -69,6 +69,10 @@ def lib() -> C.CDLL:
         L.ora_min_unique_list.restype = C.c_int
         L.ora_min_unique_list.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_uint64, u32p, C.c_uint32,
                                           C.c_int, C.c_int, u32p, i64p, u64p, u64p]
+        L.ora_min_unique_multi.restype = C.c_int
+        L.ora_min_unique_multi.argtypes = [C.POINTER(C.c_void_p), C.c_uint32, C.POINTER(C.c_void_p), C.c_uint32,
+                                           C.c_uint64, C.c_uint64, C.c_int, u32p, C.c_uint32, C.c_uint32, C.c_int,
+                                           u32p, i64p, u64p, u64p]
         _lib = L
     return _lib
 
@@ -174,6 +178,50 @@ class OracleIndex:
             p, ln = int(zero[0]), int(zero[1])
             raise ZeroCount(zero_count_message(bytes(seg[p:p + ln]).decode("utf-8")))
         return out[:num_kmers]
+
+
+class ShortCount(RuntimeError):
+    """A summed count below the number of sequences that is not 0: the reference's range loop never ends."""
+
+
+def min_unique_multi_segment(indexes: list, segs: list, num_kmers: int, kmer_lengths, is_range: bool,
+                             initial_search_length: int = 0, use_rc: bool = True) -> np.ndarray:
+    """Several sequences x several indexes for one tuple of segment buffers (search.py:383-644 with
+    count == num_sequences, :656-697)."""
+    bufs = [np.frombuffer(s, dtype=np.uint8) for s in segs]
+    assert all(b.size == bufs[0].size for b in bufs)
+    ih = (C.c_void_p * len(indexes))(*[ix._h for ix in indexes])
+    sp = (C.c_void_p * len(bufs))(*[b.ctypes.data for b in bufs])
+    kl = np.ascontiguousarray([min(kmer_lengths), max(kmer_lengths)] if is_range else list(kmer_lengths), dtype=np.uint32)
+    out = np.zeros(max(num_kmers, 1), dtype=np.uint32)
+    zero = np.full(3, -1, dtype=np.int64)
+    steps, queries = C.c_uint64(0), C.c_uint64(0)
+    r = lib().ora_min_unique_multi(ih, len(indexes), sp, len(bufs), bufs[0].size, num_kmers, int(is_range),
+                                   _ptr(kl, C.c_uint32), kl.size, initial_search_length, int(use_rc),
+                                   _ptr(out, C.c_uint32), _ptr(zero, C.c_int64), C.byref(steps), C.byref(queries))
+    if r < 0:
+        raise ValueError(f"oracle: invalid search arguments (code {r})")
+    if zero[0] >= 0:
+        p, ln = int(zero[0]), int(zero[1])
+        raise ZeroCount(zero_count_message(bytes(segs[0][p:p + ln]).decode("utf-8")))
+    if r == 1:
+        raise ShortCount("summed count below the number of sequences")
+    return out[:num_kmers]
+
+
+def min_unique_multi(fasta_paths: list, indexes: list, kmer_lengths, is_range: bool, kmer_batch_size: int,
+                     initial_search_length: int = 0, use_rc: bool = True) -> dict:
+    """{sequence id of the first file: array} for several FASTA / index files (search.py:222-357, zip(*sequences))."""
+    max_k = max(kmer_lengths)
+    dt = out_dtype(max_k)
+    out: dict[bytes, list] = {}
+    for tup in zip(*[segments(p, kmer_batch_size, max_k - 1) for p in fasta_paths]):
+        seg = tup[0]
+        n = len(seg.data) if seg.epilogue else len(seg.data) - (max_k - 1)
+        vals = min_unique_multi_segment(indexes, [t.data for t in tup], n, kmer_lengths, is_range,
+                                        initial_search_length, use_rc)
+        out.setdefault(seg.id, []).append(vals.astype(dt))
+    return {k: np.concatenate(v) for k, v in out.items()}
 
 
 def upper_bounds(mask, seg_len: int, max_k: int) -> np.ndarray:

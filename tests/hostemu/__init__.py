@@ -32,8 +32,27 @@ def lib():
                                 C.c_void_p, C.c_void_p]
         L.emu_min_unique.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_int, C.c_void_p, C.c_uint32,
                                      C.c_uint32, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32]
+        L.emu_min_unique_multi.argtypes = [C.POINTER(C.c_void_p), C.c_uint32, C.POINTER(C.c_void_p), C.c_uint32, C.c_uint32,
+                                           C.c_uint32, C.c_int, C.c_void_p, C.c_uint32, C.c_uint32, C.c_int, C.c_int,
+                                           C.c_void_p, C.c_void_p]
         _lib = L
     return _lib
+
+
+def min_unique_multi_segment(indexes: list, segs: list, num_kmers, kmer_lengths, is_range, initial=0, use_rc=True,
+                             out_width=4):
+    """trajectory_multi_thread over one tuple of segment buffers: (values, stats)."""
+    bufs = [np.frombuffer(s, dtype=np.uint8) for s in segs]
+    ih = (C.c_void_p * len(indexes))(*[ix._h for ix in indexes])
+    sp = (C.c_void_p * len(bufs))(*[b.ctypes.data for b in bufs])
+    kl = np.array([min(kmer_lengths), max(kmer_lengths)] if is_range else list(kmer_lengths), dtype=np.uint32)
+    out = np.zeros(max(num_kmers, 1), dtype={1: np.uint8, 2: np.uint16, 4: np.uint32}[out_width])
+    stats = np.zeros(8, dtype=np.int64)
+    r = lib().emu_min_unique_multi(ih, len(indexes), sp, len(bufs), bufs[0].size, num_kmers, 0 if is_range else 1,
+                                   kl.ctypes.data, kl.size, initial, int(use_rc), out_width, out.ctypes.data,
+                                   stats.ctypes.data)
+    assert r == 0
+    return out[:num_kmers], stats
 
 
 class EmuIndex:

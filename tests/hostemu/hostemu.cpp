@@ -160,4 +160,42 @@ int emu_min_unique(EmuIndex *ix, const uint8_t *seg, uint32_t seg_len, uint32_t 
   return 0;
 }
 
+// nm_workspace_multi + nm_workspace_search: several sequences x several indexes on the reference's trajectory.
+// stats: [0] lf, [1] queries, [2] short counts, [4] zero pos (-1), [5] zero len, [6] zero round
+int emu_min_unique_multi(EmuIndex *const *ixs, uint32_t n_ix, const uint8_t *const *segs, uint32_t n_seq, uint32_t seg_len,
+                         uint32_t num_kmers, int mode, const uint32_t *klist, uint32_t nk, uint32_t initial, int use_rc,
+                         int out_width, void *out, int64_t *stats) {
+  if (n_ix == 0 || n_ix > kMaxMulti || n_seq == 0 || n_seq > kMaxMulti) return -1;
+  std::vector<uint8_t> codes(seg_len + 16);
+  std::vector<uint32_t> seedkey(seg_len + 1), nb(seg_len + 1), tf((seg_len + kTile - 1) / kTile + 1), G(seg_len + 2), R(seg_len + 1);
+  unsigned long long ctr[CTR_N] = {0, 0, 0, 0, ~0ull, 0, 0, 0};
+  SegParams P{};
+  P.seg = segs[0]; P.codes = codes.data(); P.seedkey = seedkey.data(); P.nb = nb.data(); P.tile_first = tf.data();
+  P.G = G.data(); P.R = R.data(); P.out = out; P.klist = klist; P.counters = ctr;
+  P.seg_len = seg_len; P.num_kmers = num_kmers; P.nk = nk; P.initial = initial; P.mode = mode;
+  P.use_rc = use_rc; P.out_width = out_width; P.gsize = 16;
+  if (mode == 0) { P.kmin = klist[0]; P.kmax = klist[1]; }
+  else { P.kmin = P.kmax = klist[0]; for (uint32_t j = 0; j < nk; ++j) { if (klist[j] < P.kmin) P.kmin = klist[j]; if (klist[j] > P.kmax) P.kmax = klist[j]; } }
+  const DevIndex &d0 = ixs[0]->dev;
+  P.sl = d0.seed_len; P.seedtab = d0.seed32; P.seedpair = nullptr; P.dcap = P.sl + 12;
+  for (uint32_t p = 0; p < seg_len; ++p) prep_thread(d0, P, p);
+  const uint32_t ntiles = (seg_len + kTile - 1) / kTile;
+  for (uint32_t t = 0; t < ntiles; ++t) nb_tile_thread(P, t);
+  MultiSet M{};
+  M.n_ix = n_ix; M.n_seq = n_seq;
+  for (uint32_t x = 0; x < n_ix; ++x) M.ix[x] = ixs[x]->dev;
+  for (uint32_t j = 0; j < n_seq; ++j) M.seg[j] = segs[j];
+  uint32_t steps = 0, nq = 0, nshort = 0;
+  for (uint32_t i = 0; i < num_kmers; ++i) trajectory_multi_thread(M, P, i, steps, nq, nshort);
+  if (stats) {
+    stats[0] = steps; stats[1] = nq; stats[2] = nshort; stats[3] = 0; stats[4] = -1; stats[5] = 0; stats[6] = -1; stats[7] = 0;
+    if (ctr[CTR_ZERO_KEY] != ~0ull) {
+      stats[4] = (int64_t)(ctr[CTR_ZERO_KEY] & 0xFFFFFFFFull);
+      stats[6] = (int64_t)(ctr[CTR_ZERO_KEY] >> 32);
+      stats[5] = G[stats[4]];
+    }
+  }
+  return 0;
+}
+
 }  // extern "C"

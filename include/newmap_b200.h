@@ -145,6 +145,9 @@ int nm_workspace_sync(nm_workspace *ws, nm_stats *stats);
 #define NM_OPT_GSIZE 3    /* positions per certificate group; 0 = 16 */
 #define NM_OPT_PASS1 4    /* kernel of the first pass: 0 = chosen from the seed depth in use (default), 1 = one thread per
                              position, 2 = tiled (seed lookups batched, lanes refilled from a queue) */
+#define NM_OPT_GSIZE2 5   /* positions per group of the coarse certificate round that runs before the fine one (one chain,
+                             that much deeper, settles the inside of long exact repeats: fewer LF steps, longer critical path);
+                             default 0 = no coarse round, as is any value below 32 */
 int nm_workspace_option(nm_workspace *ws, int option, uint64_t value);
 /* 64-bit FNV-style checksum of the last search's output computed on the device (for
  * device-resident runs that never copy the output back). */

@@ -249,16 +249,14 @@ NM_HD uint32_t occ_in_block(const Rank32Block &b, unsigned letter, uint32_t off)
 NM_HD void lf_fast(const DevIndex &ix, const uint32_t *C32, unsigned letter, uint32_t &lo, uint32_t &hi) {
   if (letter < 4u) {
     const uint32_t blo = lo >> 6, bhi = hi >> 6;
+    // both loads are issued before either is used: a chain is a sequence of DEPENDENT steps, and a step whose bounds
+    // lie in two blocks must cost one memory latency, not two
     const Rank32Block a = ld_rank32(ix.rank32, blo);
-    uint32_t nlo = occ_in_block(a, letter, lo & 63u), nhi;
-    bool poison = a.c[0] == kPoison;
-    if (bhi == blo) {
-      nhi = occ_in_block(a, letter, hi & 63u);
-    } else {
-      const Rank32Block b = ld_rank32(ix.rank32, bhi);
-      nhi = occ_in_block(b, letter, hi & 63u);
-      poison = poison || b.c[0] == kPoison;
-    }
+    Rank32Block b = a;
+    if (bhi != blo) b = ld_rank32(ix.rank32, bhi);
+    const uint32_t nlo = occ_in_block(a, letter, lo & 63u);
+    const uint32_t nhi = occ_in_block(b, letter, hi & 63u);
+    const bool poison = a.c[0] == kPoison || b.c[0] == kPoison;
     if (!poison) {
       const uint32_t c = C32[letter];
       lo = c + nlo;
@@ -360,6 +358,7 @@ struct SegParams {
   int want_ref_lf;
   uint32_t dcap;   // first-pass depth cap of the trajectory-free search (characters, > seed_len)
   uint32_t gsize;  // positions per certificate group of the deep pass
+  uint32_t own_chains;  // chains of their own a certificate thread may run for positions no bound settles
 };
 
 NM_HD void store_out(const SegParams &P, uint32_t i, uint32_t v) {
@@ -723,6 +722,40 @@ NM_HD void free_chain_thread(const DevIndex &ix, const uint32_t *C32, const SegP
   }
 }
 
+// What the chain r run from the end e0 says about a deep end e <= e0 by itself and by containment; true when G[e]
+// was settled (written), false when it stays deep
+NM_HD bool cert_contain_fwd(const SegParams &P, const ChainResult &r, uint32_t e0, uint32_t e) {
+  const uint32_t dt = e0 - e;
+  uint32_t L = P.kmax;                             // deepest length e itself may be asked about
+  if (r.wall && r.d_stop > dt && r.d_stop - dt < L) L = r.d_stop - dt;
+  if (dt == 0) {
+    P.G[e] = (r.d_hit && r.d_hit <= L) ? r.d_hit : kNone;
+    return true;
+  }
+  const bool beyond_wall = r.wall && r.d_stop <= dt;  // e lies beyond the wall e0's chain ran into
+  if (!beyond_wall && L + dt <= r.d_stop && (r.d_hit == 0 || r.d_hit > L + dt)) {
+    P.G[e] = kNone;                                // seg[e-L, e0) occurs twice, so does seg[e-L, e)
+    return true;
+  }
+  return false;
+}
+// mirror image: the chain r run from the start i0 and a deep start i >= i0
+NM_HD bool cert_contain_rc(const SegParams &P, const ChainResult &r, uint32_t i0, uint32_t i) {
+  const uint32_t dt = i - i0;
+  uint32_t L = P.kmax;
+  if (r.wall && r.d_stop > dt && r.d_stop - dt < L) L = r.d_stop - dt;
+  if (dt == 0) {
+    P.R[i] = (r.d_hit && r.d_hit <= L) ? r.d_hit : kInf;
+    return true;
+  }
+  const bool beyond_wall = r.wall && r.d_stop <= dt;
+  if (!beyond_wall && L + dt <= r.d_stop && (r.d_hit == 0 || r.d_hit > L + dt)) {
+    P.R[i] = kInf;                                 // rc(seg[i0, i+L)) still occurs, so does rc(seg[i, i+L))
+    return true;
+  }
+  return false;
+}
+
 // pass 2: group t covers ends e in (t*gs, (t+1)*gs] and starts i in [t*gs, (t+1)*gs)
 // (parts: bit 0 = the forward-strand half, bit 1 = the other-strand half; the kernel gives each half its own thread
 // so that the two long chains of a group run side by side)
@@ -742,21 +775,12 @@ NM_HD void free_cert_thread(const DevIndex &ix, const uint32_t *C32, const SegPa
       // nu: the deepest explored length at which seg[e0-nu, e0) still occurs at least twice (e0 was kDeep, so the
       // chain got beyond the first pass's cap before it could hit)
       const uint32_t nu = r.d_hit ? r.d_hit - 1u : r.d_stop;
-      uint32_t budget = kCertOwnChains;
+      uint32_t budget = P.own_chains;
       for (uint32_t e = emin; e <= e0; ++e) {
         if (P.G[e] != kDeep) continue;
         const uint32_t dt = e0 - e;
-        uint32_t L = P.kmax;                             // deepest length e itself may be asked about
-        if (r.wall && r.d_stop > dt && r.d_stop - dt < L) L = r.d_stop - dt;
-        if (dt == 0) {
-          P.G[e] = (r.d_hit && r.d_hit <= L) ? r.d_hit : kNone;
-          continue;
-        }
+        if (cert_contain_fwd(P, r, e0, e)) continue;
         const bool beyond_wall = r.wall && r.d_stop <= dt;  // e lies beyond the wall e0's chain ran into
-        if (!beyond_wall && L + dt <= r.d_stop && (r.d_hit == 0 || r.d_hit > L + dt)) {
-          P.G[e] = kNone;                                // seg[e-L, e0) occurs twice, so does seg[e-L, e)
-          continue;
-        }
         // seg[e-l, e) lies inside seg[e0-nu, e0) for l <= nu - dt, so G[e] >= nu - dt + 1; and a unique suffix of
         // length g ending at e-1 makes the suffix of length g+1 ending at e unique, so G[e] <= G[e-1] + 1.  Where the
         // two bounds meet (a run of positions since the last difference between two copies of a repeat: G grows by
@@ -788,18 +812,12 @@ NM_HD void free_cert_thread(const DevIndex &ix, const uint32_t *C32, const SegPa
     if (i0 != kNoBarrier) {
       const ChainResult r = run_rc_chain(ix, C32, P, i0, P.kmax + (imax - i0), steps, seeds);
       const uint32_t nu = r.d_hit ? r.d_hit - 1u : r.d_stop;  // rc(seg[i0, i0+nu)) still occurs
-      uint32_t budget = kCertOwnChains;
+      uint32_t budget = P.own_chains;
       for (uint32_t i = imax;; --i) {                    // right to left: R[i] <= R[i+1] + 1
         if (P.R[i] == kDeep) {
           const uint32_t dt = i - i0;
-          uint32_t L = P.kmax;
-          if (r.wall && r.d_stop > dt && r.d_stop - dt < L) L = r.d_stop - dt;
           const bool beyond_wall = r.wall && r.d_stop <= dt;
-          if (dt == 0) {
-            P.R[i] = (r.d_hit && r.d_hit <= L) ? r.d_hit : kInf;
-          } else if (!beyond_wall && L + dt <= r.d_stop && (r.d_hit == 0 || r.d_hit > L + dt)) {
-            P.R[i] = kInf;                               // rc(seg[i0, i+L)) still occurs, so does rc(seg[i, i+L))
-          } else {
+          if (!cert_contain_rc(P, r, i0, i)) {
             bool done = false;
             if (!beyond_wall && nu >= dt && i + 1 < P.seg_len) {
               const uint32_t right = P.R[i + 1];
@@ -817,6 +835,43 @@ NM_HD void free_cert_thread(const DevIndex &ix, const uint32_t *C32, const SegPa
         if (i == i0) break;
       }
     }
+  }
+}
+
+struct CoarseGroup {  // one (group, strand) of the coarse round: outermost deep entries, then the chain's result
+  uint32_t lo, hi, d_hit, d_stop, wall;
+};
+
+// Coarse round before pass 2: one chain per group of P.gsize (256) positions and strand, run that much deeper, and
+// the containment rule alone; settles the inside of long exact repeats (tandem arrays, recent duplications), where
+// every group of the fine round would otherwise pay a chain of max_k steps.  What it cannot settle stays deep.
+// part 0: forward strand, part 1: other strand.  (On the device this is k_coarse_scan / k_coarse_chain /
+// k_coarse_settle; this serial form is what tests/hostemu runs.)
+NM_HD void free_cert_coarse_group(const DevIndex &ix, const uint32_t *C32, const SegParams &P, uint32_t t, uint32_t part,
+                                  uint32_t &steps, uint32_t &seeds) {
+  const uint32_t gs = P.gsize;
+  if (part == 0u) {
+    const uint32_t first = t * gs + 1;
+    uint32_t last = first + gs - 1;
+    if (last > P.seg_len) last = P.seg_len;
+    uint32_t e0 = 0, emin = 0;
+    for (uint32_t e = first; e <= last; ++e)
+      if (P.G[e] == kDeep) { e0 = e; if (!emin) emin = e; }
+    if (!e0) return;
+    const ChainResult r = run_fwd_chain(ix, C32, P, e0, P.kmax + (e0 - emin), steps, seeds);
+    for (uint32_t e = emin; e <= e0; ++e)
+      if (P.G[e] == kDeep) cert_contain_fwd(P, r, e0, e);
+  } else if (P.use_rc) {
+    const uint32_t first = t * gs;
+    uint32_t end = first + gs;
+    if (end > P.num_kmers) end = P.num_kmers;
+    uint32_t i0 = kNoBarrier, imax = 0;
+    for (uint32_t i = first; i < end; ++i)
+      if (P.R[i] == kDeep) { if (i0 == kNoBarrier) i0 = i; imax = i; }
+    if (i0 == kNoBarrier) return;
+    const ChainResult r = run_rc_chain(ix, C32, P, i0, P.kmax + (imax - i0), steps, seeds);
+    for (uint32_t i = i0; i <= imax; ++i)
+      if (P.R[i] == kDeep) cert_contain_rc(P, r, i0, i);
   }
 }
 

@@ -71,8 +71,11 @@ struct nm_workspace {
   int algo_req = 0, algo_used = 0;
   bool timed_h2d = false, timed_d2h = false;
   void *pending_out = nullptr;
-  uint32_t opt_ref_lf = 0, opt_dcap = 0, opt_gsize = 0, opt_pass1 = 0;
+  uint32_t opt_ref_lf = 0, opt_dcap = 0, opt_gsize = 0, opt_pass1 = 0, opt_gsize2 = ~0u;
   // several sequences x several indexes (nm_workspace_multi); cleared by the next upload / attach
+  nm::CoarseGroup *d_cgroups = nullptr;  // coarse certificate round: 2 per group of >= kMinGsize2 positions
+  uint32_t *d_clist = nullptr;           // listed groups; [cap] = their number
+  uint64_t cgroup_cap = 0;
   nm::MultiSet *d_multi = nullptr;
   uint8_t *d_extra[nm::kMaxMulti]{};  // extra sequences' segments, max_seg_len + 16 bytes each, allocated on demand
   uint32_t multi_ix = 0, multi_seq = 0;
@@ -267,6 +270,8 @@ int load_index(const char *path, int device, nm_index **out) {
   return NM_OK;
 }
 
+constexpr uint32_t kMinGsize2 = 32;  // smallest group of the coarse certificate round (sizes its buffers)
+
 int ws_alloc(nm_workspace *ws) {
   const uint64_t n = ws->max_seg_len;
   const uint64_t ntiles = (n + nm::kTile - 1) / nm::kTile + 1;
@@ -278,6 +283,9 @@ int ws_alloc(nm_workspace *ws) {
   NM_CUDA(cudaMalloc((void **)&ws->d_G, (n + 2) * 4));
   NM_CUDA(cudaMalloc((void **)&ws->d_R, (n + 1) * 4));
   NM_CUDA(cudaMalloc(&ws->d_out, (n + 1) * 4));
+  ws->cgroup_cap = 2 * ((n + 1) / kMinGsize2 + 2);
+  NM_CUDA(cudaMalloc((void **)&ws->d_cgroups, ws->cgroup_cap * sizeof(nm::CoarseGroup)));
+  NM_CUDA(cudaMalloc((void **)&ws->d_clist, (ws->cgroup_cap + 1) * 4));
   NM_CUDA(cudaMalloc((void **)&ws->d_counters, nm::CTR_N * 8));
   NM_CUDA(cudaHostAlloc((void **)&ws->h_counters, nm::CTR_N * 8, cudaHostAllocDefault));
   for (auto &e : ws->ev) NM_CUDA(cudaEventCreate(&e));
@@ -319,7 +327,24 @@ int run_search(nm_workspace *ws, int algo) {
       ++ws->launches;
     }
     NM_CUDA(cudaEventRecord(ws->ev[EV_PASS1], st));
-    if (deep_passes) { nm::launch_free_cert(ix->dev, P, st); ++ws->launches; }
+    if (deep_passes) {
+      // coarse round first: one chain per `gsize2` positions and strand, run that much deeper, settles the inside of long exact
+      // repeats (tandem arrays, recent duplications) where every group of the fine round would otherwise pay a chain
+      // of max_k steps; what it cannot settle stays deep for the fine round
+      // Off by default: it removes a third of the LF steps of a segment (3.1 -> 2.1 per position on the 1 Gbp bench
+      // genome) but its chains are max_k + gsize2 DEPENDENT steps at about 1.5 us each, longer than everything it saves
+      // when the kernels of a segment run one after the other (profiles/r1_gsize2_sweep_c3_1g.jsonl).
+      const uint32_t g2 = ws->opt_gsize2 == ~0u ? 0u : ws->opt_gsize2;
+      if (g2 > P.gsize && g2 >= kMinGsize2) {
+        nm::SegParams Pc = P;
+        Pc.gsize = g2;
+        Pc.own_chains = 0;
+        nm::launch_free_cert_coarse(ix->dev, Pc, ws->d_cgroups, ws->d_clist, ws->d_clist + ws->cgroup_cap, st);
+        ws->launches += 3;
+      }
+      nm::launch_free_cert(ix->dev, P, st);
+      ++ws->launches;
+    }
     NM_CUDA(cudaEventRecord(ws->ev[EV_CERT1], st));
     if (deep_passes) { nm::launch_free_chain(ix->dev, P, false, st); ++ws->launches; }
     NM_CUDA(cudaEventRecord(ws->ev[EV_SEARCH1], st));
@@ -460,6 +485,7 @@ int nm_workspace_create(nm_index *ix, uint64_t max_seg_len, void *cuda_stream, n
   if (!ws) return NM_EALLOC;
   ws->ix = ix;
   ws->max_seg_len = max_seg_len;
+  if (const char *v = getenv("NEWMAP_B200_GSIZE2")) ws->opt_gsize2 = (uint32_t)strtoul(v, nullptr, 10);  // tuning experiments
   if (cuda_stream) {
     ws->stream = (cudaStream_t)cuda_stream;
   } else {
@@ -492,6 +518,8 @@ void nm_workspace_destroy(nm_workspace *ws) {
   cudaFree(ws->d_out);
   cudaFree(ws->d_klist);
   cudaFree(ws->d_multi);
+  cudaFree(ws->d_cgroups);
+  cudaFree(ws->d_clist);
   for (auto *p : ws->d_extra) cudaFree(p);
   cudaFree(ws->d_counters);
   if (ws->h_counters) cudaFreeHost(ws->h_counters);
@@ -637,6 +665,7 @@ int nm_workspace_search(nm_workspace *ws, uint64_t num_kmers, int mode, const ui
     P.dcap = ws->opt_dcap ? ws->opt_dcap : (deep ? sl + 8 : sl + 12);
     if (P.dcap <= sl) P.dcap = sl + 1;
     P.gsize = ws->opt_gsize ? ws->opt_gsize : 16;
+    P.own_chains = nm::kCertOwnChains;
   }
   if (ws->multi_ix) algo = NM_ALGO_TRAJECTORY;  // the summed count is searched on the reference's own trajectory
   ws->algo_req = algo;
@@ -743,6 +772,7 @@ int nm_workspace_option(nm_workspace *ws, int option, uint64_t value) {
     case NM_OPT_DCAP: ws->opt_dcap = (uint32_t)value; return NM_OK;
     case NM_OPT_PASS1: if (value > 2) return NM_EARG; ws->opt_pass1 = (uint32_t)value; return NM_OK;
     case NM_OPT_GSIZE: if (value > 4096) return NM_EARG; ws->opt_gsize = (uint32_t)value; return NM_OK;
+    case NM_OPT_GSIZE2: if (value > 65536) return NM_EARG; ws->opt_gsize2 = (uint32_t)value; return NM_OK;
     default: return NM_EARG;
   }
 }

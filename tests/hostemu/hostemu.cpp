@@ -103,7 +103,7 @@ int emu_count(EmuIndex *ix, const uint8_t *seq, uint64_t seq_len, const uint64_t
 // stats: [0] lf, [1] queries, [2] generic searches, [3] anomaly, [4] zero pos (-1), [5] zero len, [6] zero round, [7] ref lf
 int emu_min_unique(EmuIndex *ix, const uint8_t *seg, uint32_t seg_len, uint32_t num_kmers, int mode,
                    const uint32_t *klist, uint32_t nk, uint32_t initial, int use_rc, int algo, int out_width,
-                   void *out, int64_t *stats, uint32_t dcap, uint32_t gsize) {
+                   void *out, int64_t *stats, uint32_t dcap, uint32_t gsize, uint32_t gsize2) {
   std::vector<uint8_t> codes(seg_len + 16);
   std::vector<uint32_t> seedkey(seg_len + 1), nb(seg_len + 1), tf((seg_len + kTile - 1) / kTile + 1), G(seg_len + 2), R(seg_len + 1);
   unsigned long long ctr[CTR_N] = {0, 0, 0, 0, ~0ull, 0, 0, 0};
@@ -113,6 +113,7 @@ int emu_min_unique(EmuIndex *ix, const uint8_t *seg, uint32_t seg_len, uint32_t 
   P.seg_len = seg_len; P.num_kmers = num_kmers; P.nk = nk; P.initial = initial; P.mode = mode;
   P.use_rc = use_rc; P.out_width = out_width;
   P.gsize = gsize ? gsize : 32;
+  P.own_chains = kCertOwnChains;
   if (mode == 0) { P.kmin = klist[0]; P.kmax = klist[1]; }
   else { P.kmin = P.kmax = klist[0]; for (uint32_t j = 0; j < nk; ++j) { if (klist[j] < P.kmin) P.kmin = klist[j]; if (klist[j] > P.kmax) P.kmax = klist[j]; } }
   // nm_lib.cu nm_workspace_search: the deeper table when every queried length reaches its depth (the estimate of the
@@ -136,8 +137,16 @@ int emu_min_unique(EmuIndex *ix, const uint8_t *seg, uint32_t seg_len, uint32_t 
     if (fast) {
       for (uint32_t p = 0; p <= seg_len; ++p) free_chain_thread(ix->dev, ix->c32, P, p, true, steps, seeds);
       if (P.dcap < P.kmax) {
-        const uint32_t ngroups = (seg_len + 1 + P.gsize - 1) / P.gsize;
         uint32_t s2 = 0;
+        if (gsize2 > P.gsize) {  // nm_lib.cu run_search: coarse round first, containment and interpolation only
+          SegParams Pc = P;
+          Pc.gsize = gsize2;
+          Pc.own_chains = 0;
+          const uint32_t nc = (seg_len + 1 + Pc.gsize - 1) / Pc.gsize;
+          for (uint32_t t = 0; t < nc; ++t)
+            for (uint32_t part = 0; part < 2; ++part) free_cert_coarse_group(ix->dev, ix->c32, Pc, t, part, s2, seeds);
+        }
+        const uint32_t ngroups = (seg_len + 1 + P.gsize - 1) / P.gsize;
         for (uint32_t t = 0; t < ngroups; ++t) free_cert_thread(ix->dev, ix->c32, P, t, s2, seeds);
         ns = s2;  // reported in stats[2]: LF steps of the certificate pass
         steps += s2;

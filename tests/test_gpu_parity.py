@@ -310,10 +310,11 @@ def test_tuning_options_do_not_change_results(nm, indexes):
     buf.array[:] = np.frombuffer(seq, dtype=np.uint8)
     out = nm.PinnedBuffer(len(seq))
     ws = nm.Workspace(ix, len(seq))
-    for dcap, gsize, pass1 in ((0, 0, 0), (0, 0, 1), (0, 0, 2), (7, 1, 2), (8, 5, 1), (13, 64, 2), (40, 200, 2), (40, 200, 1),
-                               (1000, 32, 2)):
+    for n, (dcap, gsize, pass1) in enumerate(((0, 0, 0), (0, 0, 1), (0, 0, 2), (7, 1, 2), (8, 5, 1), (13, 64, 2), (40, 200, 2),
+                                              (40, 200, 1), (1000, 32, 2), (0, 16, 0), (9, 16, 2), (9, 4, 1))):
         ws.option("dcap", dcap)
         ws.option("gsize", gsize)
+        ws.option("gsize2", (256, 0, 40, 1000)[n % 4])   # coarse certificate round: default, off, other sizes
         ws.option("pass1", pass1)     # first-pass kernel: tiled with lane refill / one thread per position
         ws.upload(buf.ptr, len(seq))
         ws.search(len(seq), kl, True, out_width=1)

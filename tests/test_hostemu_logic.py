@@ -122,9 +122,11 @@ def test_random_small_genomes_all_algorithms_agree_with_oracle(tmp_path):
                 assert np.array_equal(got, want), (trial, klist[:3], is_range, "derived seed table", batch)
 
 
-@pytest.mark.parametrize("dcap_extra,gsize", [(1, 1), (1, 5), (2, 32), (4, 64), (12, 32), (3, 200), (1000, 32)])
-def test_certificate_pass_is_exact_for_any_cap_and_group(manifest, golden_searches, dcap_extra, gsize):
-    """The depth cap and the certificate group size are tuning knobs: results never depend on them."""
+@pytest.mark.parametrize("dcap_extra,gsize,gsize2", [(1, 1, 0), (1, 5, 40), (2, 32, 0), (4, 64, 256), (12, 32, 33), (3, 200, 0),
+                                                      (1000, 32, 64), (2, 16, 256), (1, 3, 1000), (4, 16, 64)])
+def test_certificate_pass_is_exact_for_any_cap_and_group(manifest, golden_searches, dcap_extra, gsize, gsize2):
+    """The depth cap, the certificate group size and the group size of the coarse certificate round are tuning knobs:
+    results never depend on them."""
     cache = {}
     for run in manifest["searches"]:
         if run["index"].startswith("genome"):
@@ -135,7 +137,8 @@ def test_certificate_pass_is_exact_for_any_cap_and_group(manifest, golden_search
         got = {}
         for seg, n in _segments(run):
             out, stats = ix.min_unique_segment(seg.data, n, klist, run["range"], run.get("initial", 0),
-                                               not run.get("norc", False), 0, dcap=seed + dcap_extra, gsize=gsize)
+                                               not run.get("norc", False), 0, dcap=seed + dcap_extra, gsize=gsize,
+                                               gsize2=gsize2)
             got.setdefault(seg.id, []).append(out)
         for sid, parts in got.items():
             want = golden_searches[f"run{run['id']}|{sid.decode()}"]
@@ -241,6 +244,7 @@ def test_diverged_repeats_interpolation_certificate(tmp_path):
                 m = len(seg.data) if seg.epilogue else len(seg.data) - (max(klist) - 1)
                 want = o.min_unique_segment(seg.data, m, klist, True, nthreads=1)
                 for dcap_extra, gsize in ((1, 32), (3, 8), (2, 64), (6, 5), (1, 1)):
-                    got, st = e.min_unique_segment(seg.data, m, klist, True, algo=0, dcap=seed + 2 + dcap_extra, gsize=gsize)
+                    got, st = e.min_unique_segment(seg.data, m, klist, True, algo=0, dcap=seed + 2 + dcap_extra, gsize=gsize,
+                                                   gsize2=(0, 48, 256)[(dcap_extra + gsize) % 3])
                     bad = np.nonzero(got != want)[0]
                     assert bad.size == 0, (trial, batch, dcap_extra, gsize, bad[:10], got[bad[:10]], want[bad[:10]])

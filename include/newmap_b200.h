@@ -148,6 +148,8 @@ int nm_workspace_sync(nm_workspace *ws, nm_stats *stats);
 #define NM_OPT_GSIZE2 5   /* positions per group of the coarse certificate round that runs before the fine one (one chain,
                              that much deeper, settles the inside of long exact repeats: fewer LF steps, longer critical path);
                              default 0 = no coarse round, as is any value below 32 */
+#define NM_OPT_OWN_CHAINS 6 /* chains of its own a certificate thread may run for a position no bound settles (the rest
+                             goes to the third pass); default 1 */
 int nm_workspace_option(nm_workspace *ws, int option, uint64_t value);
 /* 64-bit FNV-style checksum of the last search's output computed on the device (for
  * device-resident runs that never copy the output back). */

@@ -703,17 +703,18 @@ NM_HD bool rc_wanted(const SegParams &P, uint32_t i) {
 }
 
 // pass 1 and pass 3 share this: `cap` = P.dcap in pass 1, kmax in pass 3 (which only redoes kDeep entries)
+// (parts: bit 0 = the forward-strand chain ending at p, bit 1 = the other-strand chain starting at p)
 NM_HD void free_chain_thread(const DevIndex &ix, const uint32_t *C32, const SegParams &P, uint32_t p, bool first,
-                             uint32_t &steps, uint32_t &seeds) {
+                             uint32_t &steps, uint32_t &seeds, uint32_t parts = 3u) {
   const uint32_t cap = first ? (P.dcap < P.kmax ? P.dcap : P.kmax) : P.kmax;
-  if (first || P.G[p] == kDeep) {
+  if ((parts & 1u) && (first || P.G[p] == kDeep)) {
     uint32_t g = kNone;
     if (fwd_wanted(P, p)) {
       g = chain_value(P, run_fwd_chain(ix, C32, P, p, cap, steps, seeds), cap, kNone);
     }
     P.G[p] = g;
   }
-  if (p < P.seg_len && (first || P.R[p] == kDeep)) {
+  if ((parts & 2u) && p < P.seg_len && (first || P.R[p] == kDeep)) {
     uint32_t rr = kInf;
     if (rc_wanted(P, p)) {
       rr = chain_value(P, run_rc_chain(ix, C32, P, p, cap, steps, seeds), cap, kInf);

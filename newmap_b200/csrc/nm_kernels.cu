@@ -172,6 +172,7 @@ __device__ __forceinline__ const uint32_t *stage_c32(const DevIndex &ix, uint32_
 __global__ void __launch_bounds__(kBlock, 8) k_free_chain(DevIndex ix, SegParams P, bool first) {
   __shared__ uint32_t sC[8];
   const uint32_t *C32 = stage_c32(ix, sC);
+  // (giving the two chains of a position to different warps in pass 3 was measured slower: 0.134 against 0.110 ms)
   const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
   uint32_t steps = 0, seeds = 0;
   if (p <= P.seg_len) free_chain_thread(ix, C32, P, p, first, steps, seeds);

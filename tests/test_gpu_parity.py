@@ -314,7 +314,8 @@ def test_tuning_options_do_not_change_results(nm, indexes):
                                               (40, 200, 1), (1000, 32, 2), (0, 16, 0), (9, 16, 2), (9, 4, 1))):
         ws.option("dcap", dcap)
         ws.option("gsize", gsize)
-        ws.option("gsize2", (256, 0, 40, 1000)[n % 4])   # coarse certificate round: default, off, other sizes
+        ws.option("gsize2", (256, 0, 40, 1000)[n % 4])   # coarse certificate round: on, off (default), other sizes
+        ws.option("own_chains", (1, 0, 3)[n % 3])
         ws.option("pass1", pass1)     # first-pass kernel: tiled with lane refill / one thread per position
         ws.upload(buf.ptr, len(seq))
         ws.search(len(seq), kl, True, out_width=1)

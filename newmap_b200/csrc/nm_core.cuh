@@ -963,13 +963,17 @@ NM_HD void resolve_thread(const DevIndex &ix, const SegParams &P, uint32_t i, ui
       if (lim >= P.kmin) {
         if (r != kInf) {
           const uint32_t k0 = r > P.kmin ? r : P.kmin;
-          if (k0 <= lim && fwd_unique(P, i, i + lim)) {
-            uint32_t lo = i + k0, hi = i + lim;
-            while (lo < hi) {
-              const uint32_t mid = lo + (hi - lo) / 2;
-              if (fwd_unique(P, i, mid)) hi = mid; else lo = mid + 1;
+          if (k0 <= lim) {
+            if (fwd_unique(P, i, i + k0)) {              // most positions: unique at the shortest length they may have
+              ans = k0;
+            } else if (k0 < lim && fwd_unique(P, i, i + lim)) {
+              uint32_t lo = i + k0 + 1, hi = i + lim;
+              while (lo < hi) {
+                const uint32_t mid = lo + (hi - lo) / 2;
+                if (fwd_unique(P, i, mid)) hi = mid; else lo = mid + 1;
+              }
+              ans = lo - i;
             }
-            ans = lo - i;
           }
         }
         if (P.want_ref_lf) ref_lf += ref_trajectory_steps(P, ix.seed_len, lim, ans, P.use_rc ? r : 0u);

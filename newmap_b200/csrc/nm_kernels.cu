@@ -73,33 +73,53 @@ __global__ void __launch_bounds__(kBlock) k_prep(DevIndex ix, SegParams P) {
   const bool live = p0 < P.seg_len;
   uint32_t first_barrier = kNoBarrier;
   unsigned long long cw = 0;  // the thread's 8 codes, one per byte (no dynamically indexed arrays: no local memory)
-  if (live) {
+  // the block's codes, each computed once, + the sl - 1 codes after them the last windows reach into
+  __shared__ unsigned long long s_code[kBlock + 2];
+  {
+    const uint64_t b0 = (uint64_t)blockIdx.x * blockDim.x * kPrepV;
+    if (live) {
 #pragma unroll
-    for (int j = 0; j < kPrepV; ++j) {
-      const uint8_t cj = (p0 + j < P.seg_len) ? code_of(P, (uint32_t)(p0 + j)) : (uint8_t)kIrregular;
-      cw |= (unsigned long long)cj << (8 * j);
+      for (int j = 0; j < kPrepV; ++j) {
+        const uint8_t cj = (p0 + j < P.seg_len) ? code_of(P, (uint32_t)(p0 + j)) : (uint8_t)kIrregular;
+        cw |= (unsigned long long)cj << (8 * j);
+      }
+    } else {
+      cw = ~0ull;  // beyond the segment: irregular, invalidates every window that reaches it
     }
-    auto code_at = [&](uint32_t j) -> uint32_t {  // code of position p0 + j (beyond the segment: invalidates the window)
-      if (j < kPrepV) return (uint32_t)(cw >> (8 * j)) & 0xFFu;
-      return (p0 + j < P.seg_len) ? (uint32_t)code_of(P, (uint32_t)(p0 + j)) : (uint32_t)kIrregular;
-    };
+    s_code[threadIdx.x] = cw;
+    if (threadIdx.x < 16) {
+      const uint64_t q = b0 + (uint64_t)kBlock * kPrepV + threadIdx.x;
+      reinterpret_cast<uint8_t *>(s_code + kBlock)[threadIdx.x] =
+          (q < P.seg_len) ? code_of(P, (uint32_t)q) : (uint8_t)kIrregular;
+    }
+    __syncthreads();
+    if (!live) cw = 0;
+  }
+  if (live) {
     // rolling seed key; `bad` = characters still to shift out before the window is free of irregular /
     // barrier / out-of-range characters
+    const unsigned long long w1 = s_code[threadIdx.x + 1], w2 = s_code[threadIdx.x + 2];
+    auto code_at = [&](uint32_t j) -> uint32_t {  // code of position p0 + j, j < 24
+      const unsigned long long w = j < 8u ? cw : (j < 16u ? w1 : w2);
+      return (uint32_t)(w >> (8u * (j & 7u))) & 0xFFu;
+    };
     uint32_t key = 0, bad = 0;
     const uint32_t keymask = (sl >= 16) ? 0xFFFFFFFFu : ((1u << (2 * sl)) - 1u);
     auto push = [&](uint32_t j) {
       const uint32_t cj = code_at(j);
       key = ((key << 2) | (cj & 3u)) & keymask;
-      bad = (p0 + j >= P.seg_len || (cj & (kIrregular | kBarrier))) ? sl : (bad ? bad - 1 : 0);
+      bad = (cj & (kIrregular | kBarrier)) ? sl : (bad ? bad - 1 : 0);
     };
     for (uint32_t j = 0; j + 1 < sl; ++j) push(j);
     uint32_t keys[kPrepV];
+    unsigned long long badbits = 0;
 #pragma unroll
     for (int i = 0; i < kPrepV; ++i) {
       push(sl - 1 + i);
       keys[i] = bad ? 0u : key;
-      if (bad) cw |= (unsigned long long)kSeedBad << (8 * i);  // after code_at(j < kPrepV) has been consumed: push() only
-    }                                                           // reads the letter / irregular / barrier bits of cw
+      if (bad) badbits |= (unsigned long long)kSeedBad << (8 * i);
+    }
+    cw |= badbits;
     if (p0 + kPrepV <= P.seg_len) {
       *reinterpret_cast<uint2 *>(P.codes + p0) = make_uint2((uint32_t)cw, (uint32_t)(cw >> 32));
       uint4 *kd = reinterpret_cast<uint4 *>(P.seedkey + p0);

@@ -150,6 +150,8 @@ int nm_workspace_sync(nm_workspace *ws, nm_stats *stats);
                              default 0 = no coarse round, as is any value below 32 */
 #define NM_OPT_OWN_CHAINS 6 /* chains of its own a certificate thread may run for a position no bound settles (the rest
                              goes to the third pass); default 1 */
+#define NM_OPT_STALL 7    /* first pass: a chain whose interval kept its size for this many steps in a row is left to the
+                             later passes at once instead of at the depth cap (it is inside a repeat); default 0 = off */
 int nm_workspace_option(nm_workspace *ws, int option, uint64_t value);
 /* 64-bit FNV-style checksum of the last search's output computed on the device (for
  * device-resident runs that never copy the output back). */

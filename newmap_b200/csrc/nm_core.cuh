@@ -359,6 +359,7 @@ struct SegParams {
   uint32_t dcap;   // first-pass depth cap of the trajectory-free search (characters, > seed_len)
   uint32_t gsize;  // positions per certificate group of the deep pass
   uint32_t own_chains;  // chains of their own a certificate thread may run for positions no bound settles
+  uint32_t stall;       // first pass: a chain whose interval kept its size for this many steps in a row is left deep (0 = off)
 };
 
 NM_HD void store_out(const SegParams &P, uint32_t i, uint32_t v) {
@@ -674,6 +675,19 @@ NM_HD bool chain_iterate(const DevIndex &ix, const uint32_t *C32, const SegParam
   return false;
 }
 
+// First pass only.  A chain whose interval has kept its size for P.stall steps in a row is almost surely inside a
+// repeat (two random 16-letter matches part ways within a step or two; the copies of a repeat stay together) and
+// would run on to the depth cap only to be marked deep there: it is marked deep now.  Deep entries are settled
+// exactly by passes 2 and 3 whatever made them deep, so this moves work, never a result.
+struct StallState {
+  uint32_t n, run;
+};
+NM_HD bool chain_stalled(const SegParams &P, StallState &st, const ChainState &s) {
+  const uint32_t n = s.hi - s.lo;
+  st.run = (n == st.n) ? st.run + 1u : 0u;
+  st.n = n;
+  return P.stall && st.run >= P.stall;
+}
 NM_HD ChainResult run_chain(const DevIndex &ix, const uint32_t *C32, const SegParams &P, uint32_t kind, uint32_t p,
                             uint32_t maxdepth, uint32_t &steps, uint32_t &seeds) {
   ChainState s = chain_init(C32, P, kind, p, seeds);
@@ -697,6 +711,17 @@ NM_HD uint32_t chain_value(const SegParams &P, const ChainResult &r, uint32_t ca
   return none;
 }
 
+// the first pass's chain for (kind, p): value for G / R
+NM_HD uint32_t run_chain_pass1(const DevIndex &ix, const uint32_t *C32, const SegParams &P, uint32_t kind, uint32_t p,
+                               uint32_t cap, uint32_t none, uint32_t &steps, uint32_t &seeds) {
+  ChainState s = chain_init(C32, P, kind, p, seeds);
+  StallState st{s.hi - s.lo, 0u};
+  ChainResult r{0, 0, false};
+  while (!chain_iterate(ix, C32, P, kind, p, s, cap, steps, r))
+    if (chain_stalled(P, st, s)) return kDeep;
+  return chain_value(P, r, cap, none);
+}
+
 NM_HD bool fwd_wanted(const SegParams &P, uint32_t e) { return e >= 1 && !(P.codes[e - 1] & kBarrier); }
 NM_HD bool rc_wanted(const SegParams &P, uint32_t i) {
   return P.use_rc && i < P.num_kmers && !(P.codes[i] & kNoStart);
@@ -710,14 +735,16 @@ NM_HD void free_chain_thread(const DevIndex &ix, const uint32_t *C32, const SegP
   if ((parts & 1u) && (first || P.G[p] == kDeep)) {
     uint32_t g = kNone;
     if (fwd_wanted(P, p)) {
-      g = chain_value(P, run_fwd_chain(ix, C32, P, p, cap, steps, seeds), cap, kNone);
+      g = first ? run_chain_pass1(ix, C32, P, 0u, p, cap, kNone, steps, seeds)
+                : chain_value(P, run_fwd_chain(ix, C32, P, p, cap, steps, seeds), cap, kNone);
     }
     P.G[p] = g;
   }
   if ((parts & 2u) && p < P.seg_len && (first || P.R[p] == kDeep)) {
     uint32_t rr = kInf;
     if (rc_wanted(P, p)) {
-      rr = chain_value(P, run_rc_chain(ix, C32, P, p, cap, steps, seeds), cap, kInf);
+      rr = first ? run_chain_pass1(ix, C32, P, 1u, p, cap, kInf, steps, seeds)
+                 : chain_value(P, run_rc_chain(ix, C32, P, p, cap, steps, seeds), cap, kInf);
     }
     P.R[p] = rr;
   }

@@ -312,6 +312,7 @@ __global__ void __launch_bounds__(kBlock, 8) k_pass1_tiled(DevIndex ix, SegParam
   bool have = false;
   uint32_t p = 0, kind = 0;
   ChainState s{0, 0, 0};
+  StallState stall{0, 0};
   for (;;) {
     if (!have) {
       const uint32_t at = atomicAdd(&s_next, 1u);
@@ -320,11 +321,15 @@ __global__ void __launch_bounds__(kBlock, 8) k_pass1_tiled(DevIndex ix, SegParam
       p = it.x;
       s = ChainState{it.y, it.z, it.w & 0x7FFFFFFFu};
       kind = it.w >> 31;
+      stall = StallState{s.hi - s.lo, 0u};
       have = true;
     }
     ChainResult r{0, 0, false};
     if (chain_iterate(ix, C32, P, kind, p, s, cap, steps, r)) {
       *(kind == 0u ? P.G + p : P.R + p) = chain_value(P, r, cap, kind == 0u ? kNone : kInf);
+      have = false;
+    } else if (chain_stalled(P, stall, s)) {      // run_chain_pass1 (nm_core.cuh)
+      *(kind == 0u ? P.G + p : P.R + p) = kDeep;
       have = false;
     }
   }

@@ -71,7 +71,7 @@ struct nm_workspace {
   int algo_req = 0, algo_used = 0;
   bool timed_h2d = false, timed_d2h = false;
   void *pending_out = nullptr;
-  uint32_t opt_ref_lf = 0, opt_dcap = 0, opt_gsize = 0, opt_pass1 = 0, opt_gsize2 = ~0u, opt_own_chains = ~0u;
+  uint32_t opt_ref_lf = 0, opt_dcap = 0, opt_gsize = 0, opt_pass1 = 0, opt_gsize2 = ~0u, opt_own_chains = ~0u, opt_stall = ~0u;
   // several sequences x several indexes (nm_workspace_multi); cleared by the next upload / attach
   nm::CoarseGroup *d_cgroups = nullptr;  // coarse certificate round: 2 per group of >= kMinGsize2 positions
   uint32_t *d_clist = nullptr;           // listed groups; [cap] = their number
@@ -486,6 +486,7 @@ int nm_workspace_create(nm_index *ix, uint64_t max_seg_len, void *cuda_stream, n
   ws->ix = ix;
   ws->max_seg_len = max_seg_len;
   if (const char *v = getenv("NEWMAP_B200_GSIZE2")) ws->opt_gsize2 = (uint32_t)strtoul(v, nullptr, 10);  // tuning experiments
+  if (const char *v = getenv("NEWMAP_B200_STALL")) ws->opt_stall = (uint32_t)strtoul(v, nullptr, 10);
   if (const char *v = getenv("NEWMAP_B200_OWN_CHAINS")) ws->opt_own_chains = (uint32_t)strtoul(v, nullptr, 10);
   if (cuda_stream) {
     ws->stream = (cudaStream_t)cuda_stream;
@@ -667,6 +668,10 @@ int nm_workspace_search(nm_workspace *ws, uint64_t num_kmers, int mode, const ui
     if (P.dcap <= sl) P.dcap = sl + 1;
     P.gsize = ws->opt_gsize ? ws->opt_gsize : 16;
     P.own_chains = ws->opt_own_chains == ~0u ? nm::kCertOwnChains : ws->opt_own_chains;
+    // only when passes 2 and 3 will run (run_search: deep_passes).  Off by default: with 2 it removes 45 % of the first
+    // pass's LF steps on the 1 Gbp bench genome, but those are the cheap ones (neighbouring positions inside a repeat
+    // walk the same rank blocks, L2 hits) and the later passes pay more than it saves (8.45 -> 8.03 G positions/s).
+    P.stall = P.dcap < kmax ? (ws->opt_stall == ~0u ? 0u : ws->opt_stall) : 0u;
   }
   if (ws->multi_ix) algo = NM_ALGO_TRAJECTORY;  // the summed count is searched on the reference's own trajectory
   ws->algo_req = algo;
@@ -774,6 +779,7 @@ int nm_workspace_option(nm_workspace *ws, int option, uint64_t value) {
     case NM_OPT_PASS1: if (value > 2) return NM_EARG; ws->opt_pass1 = (uint32_t)value; return NM_OK;
     case NM_OPT_GSIZE: if (value > 4096) return NM_EARG; ws->opt_gsize = (uint32_t)value; return NM_OK;
     case NM_OPT_OWN_CHAINS: if (value > 64) return NM_EARG; ws->opt_own_chains = (uint32_t)value; return NM_OK;
+    case NM_OPT_STALL: if (value > 64) return NM_EARG; ws->opt_stall = (uint32_t)value; return NM_OK;
     case NM_OPT_GSIZE2: if (value > 65536) return NM_EARG; ws->opt_gsize2 = (uint32_t)value; return NM_OK;
     default: return NM_EARG;
   }

@@ -103,7 +103,7 @@ int emu_count(EmuIndex *ix, const uint8_t *seq, uint64_t seq_len, const uint64_t
 // stats: [0] lf, [1] queries, [2] generic searches, [3] anomaly, [4] zero pos (-1), [5] zero len, [6] zero round, [7] ref lf
 int emu_min_unique(EmuIndex *ix, const uint8_t *seg, uint32_t seg_len, uint32_t num_kmers, int mode,
                    const uint32_t *klist, uint32_t nk, uint32_t initial, int use_rc, int algo, int out_width,
-                   void *out, int64_t *stats, uint32_t dcap, uint32_t gsize, uint32_t gsize2) {
+                   void *out, int64_t *stats, uint32_t dcap, uint32_t gsize, uint32_t gsize2, uint32_t stall) {
   std::vector<uint8_t> codes(seg_len + 16);
   std::vector<uint32_t> seedkey(seg_len + 1), nb(seg_len + 1), tf((seg_len + kTile - 1) / kTile + 1), G(seg_len + 2), R(seg_len + 1);
   unsigned long long ctr[CTR_N] = {0, 0, 0, 0, ~0ull, 0, 0, 0};
@@ -124,6 +124,7 @@ int emu_min_unique(EmuIndex *ix, const uint8_t *seg, uint32_t seg_len, uint32_t 
   P.seedpair = deep ? ix->dev.seedx : nullptr;
   P.want_ref_lf = deep ? 0 : 1;
   P.dcap = dcap ? dcap : P.sl + 12; if (P.dcap <= P.sl) P.dcap = P.sl + 1;
+  P.stall = P.dcap < P.kmax ? stall : 0;
   for (uint32_t p = 0; p < seg_len; ++p) prep_thread(ix->dev, P, p);
   const uint32_t ntiles = (seg_len + kTile - 1) / kTile;
   for (uint32_t t = 0; t < ntiles; ++t) nb_tile_thread(P, t);

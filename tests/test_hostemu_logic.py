@@ -138,7 +138,7 @@ def test_certificate_pass_is_exact_for_any_cap_and_group(manifest, golden_search
         for seg, n in _segments(run):
             out, stats = ix.min_unique_segment(seg.data, n, klist, run["range"], run.get("initial", 0),
                                                not run.get("norc", False), 0, dcap=seed + dcap_extra, gsize=gsize,
-                                               gsize2=gsize2)
+                                               gsize2=gsize2, stall=(dcap_extra + gsize) % 4)
             got.setdefault(seg.id, []).append(out)
         for sid, parts in got.items():
             want = golden_searches[f"run{run['id']}|{sid.decode()}"]
@@ -245,6 +245,6 @@ def test_diverged_repeats_interpolation_certificate(tmp_path):
                 want = o.min_unique_segment(seg.data, m, klist, True, nthreads=1)
                 for dcap_extra, gsize in ((1, 32), (3, 8), (2, 64), (6, 5), (1, 1)):
                     got, st = e.min_unique_segment(seg.data, m, klist, True, algo=0, dcap=seed + 2 + dcap_extra, gsize=gsize,
-                                                   gsize2=(0, 48, 256)[(dcap_extra + gsize) % 3])
+                                                   gsize2=(0, 48, 256)[(dcap_extra + gsize) % 3], stall=(1, 2, 0, 3)[gsize % 4])
                     bad = np.nonzero(got != want)[0]
                     assert bad.size == 0, (trial, batch, dcap_extra, gsize, bad[:10], got[bad[:10]], want[bad[:10]])

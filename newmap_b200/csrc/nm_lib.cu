@@ -666,7 +666,7 @@ int nm_workspace_search(nm_workspace *ws, uint64_t num_kmers, int mode, const ui
     const uint32_t sl = P.sl;
     P.dcap = ws->opt_dcap ? ws->opt_dcap : (deep ? sl + 8 : sl + 12);
     if (P.dcap <= sl) P.dcap = sl + 1;
-    P.gsize = ws->opt_gsize ? ws->opt_gsize : 16;
+    P.gsize = ws->opt_gsize ? ws->opt_gsize : 20;  // profiles/r1_gsize_sweep_final_c3_1g.jsonl
     P.own_chains = ws->opt_own_chains == ~0u ? nm::kCertOwnChains : ws->opt_own_chains;
     // only when passes 2 and 3 will run (run_search: deep_passes).  Off by default: with 2 it removes 45 % of the first
     // pass's LF steps on the 1 Gbp bench genome, but those are the cheap ones (neighbouring positions inside a repeat

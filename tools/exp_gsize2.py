@@ -25,7 +25,10 @@ for seg, n in segs:
     pbs.append(pb)
 kl = list(range(20, 201))
 want = None
-for gsize, gsize2 in ((16, 0), (16, 64), (16, 128), (16, 256), (16, 512), (16, 1024), (32, 256), (32, 512), (8, 128), (8, 256)):
+PAIRS = ((16, 0), (16, 64), (16, 128), (16, 256), (16, 512), (16, 1024), (32, 256), (32, 512), (8, 128), (8, 256))
+if len(sys.argv) > 4:      # "16:0,24:0,32:0"
+    PAIRS = tuple(tuple(int(x) for x in pr.split(":")) for pr in sys.argv[4].split(","))
+for gsize, gsize2 in PAIRS:
     ws.option("gsize", gsize)
     ws.option("gsize2", gsize2)
     tot = {}

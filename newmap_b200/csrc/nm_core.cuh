@@ -866,40 +866,43 @@ NM_HD void free_cert_thread(const DevIndex &ix, const uint32_t *C32, const SegPa
   }
 }
 
-struct CoarseGroup {  // one (group, strand) of the coarse round: outermost deep entries, then the chain's result
-  uint32_t lo, hi, d_hit, d_stop, wall;
+struct CoarseGroup {  // one (group, strand) of the coarse round: result of its anchor chain
+  uint32_t d_hit, d_stop, wall;
 };
 
-// Coarse round before pass 2: one chain per group of P.gsize (256) positions and strand, run that much deeper, and
-// the containment rule alone; settles the inside of long exact repeats (tandem arrays, recent duplications), where
-// every group of the fine round would otherwise pay a chain of max_k steps.  What it cannot settle stays deep.
-// part 0: forward strand, part 1: other strand.  (On the device this is k_coarse_scan / k_coarse_chain /
-// k_coarse_settle; this serial form is what tests/hostemu runs.)
-NM_HD void free_cert_coarse_group(const DevIndex &ix, const uint32_t *C32, const SegParams &P, uint32_t t, uint32_t part,
-                                  uint32_t &steps, uint32_t &seeds) {
-  const uint32_t gs = P.gsize;
+// Coarse round: one anchor chain per group of P.gsize (256) positions and strand, run max_k + P.gsize - 1 deep, and
+// the containment rule alone.  It settles the inside of long exact repeats (tandem arrays, recent duplications), where
+// every group of the fine round would otherwise pay a chain of max_k steps.  The anchors are fixed positions -- the
+// LAST end of the group for the forward strand, the FIRST start for the other strand -- so the chains need nothing
+// from the first pass and run BESIDE it (another stream): their latency, max_k + 255 dependent steps, hides behind
+// it, and outside repeats they end after a step or two.  What the round cannot settle stays deep.
+// group t: ends e in (t*gs, (t+1)*gs], starts i in [t*gs, (t+1)*gs); part 0 forward strand, part 1 other strand.
+NM_HD uint32_t coarse_anchor(const SegParams &P, uint32_t t, uint32_t part) {
   if (part == 0u) {
-    const uint32_t first = t * gs + 1;
-    uint32_t last = first + gs - 1;
-    if (last > P.seg_len) last = P.seg_len;
-    uint32_t e0 = 0, emin = 0;
-    for (uint32_t e = first; e <= last; ++e)
-      if (P.G[e] == kDeep) { e0 = e; if (!emin) emin = e; }
-    if (!e0) return;
-    const ChainResult r = run_fwd_chain(ix, C32, P, e0, P.kmax + (e0 - emin), steps, seeds);
-    for (uint32_t e = emin; e <= e0; ++e)
-      if (P.G[e] == kDeep) cert_contain_fwd(P, r, e0, e);
-  } else if (P.use_rc) {
-    const uint32_t first = t * gs;
-    uint32_t end = first + gs;
-    if (end > P.num_kmers) end = P.num_kmers;
-    uint32_t i0 = kNoBarrier, imax = 0;
-    for (uint32_t i = first; i < end; ++i)
-      if (P.R[i] == kDeep) { if (i0 == kNoBarrier) i0 = i; imax = i; }
-    if (i0 == kNoBarrier) return;
-    const ChainResult r = run_rc_chain(ix, C32, P, i0, P.kmax + (imax - i0), steps, seeds);
-    for (uint32_t i = i0; i <= imax; ++i)
-      if (P.R[i] == kDeep) cert_contain_rc(P, r, i0, i);
+    const uint64_t e0 = ((uint64_t)t + 1u) * P.gsize;
+    return e0 > P.seg_len ? P.seg_len : (uint32_t)e0;
+  }
+  return t * P.gsize;
+}
+NM_HD CoarseGroup coarse_anchor_thread(const DevIndex &ix, const uint32_t *C32, const SegParams &P, uint32_t t, uint32_t part,
+                                       uint32_t &steps, uint32_t &seeds) {
+  const uint32_t a = coarse_anchor(P, t, part);
+  const bool wanted = part == 0u ? fwd_wanted(P, a) : rc_wanted(P, a);
+  if (!wanted) return CoarseGroup{0u, 0u, 1u};   // a wall at depth 0: says nothing about any other position
+  const ChainResult r = run_chain(ix, C32, P, part, a, P.kmax + P.gsize - 1u, steps, seeds);
+  return CoarseGroup{r.d_hit, r.d_stop, r.wall ? 1u : 0u};
+}
+// position p: the end p (forward strand) and the start p (other strand), if still deep, against their group's anchor
+NM_HD void coarse_settle_thread(const SegParams &P, const CoarseGroup *groups, uint32_t p) {
+  if (p >= 1u && p <= P.seg_len && P.G[p] == kDeep) {
+    const uint32_t t = (p - 1u) / P.gsize;
+    const CoarseGroup g = groups[2u * t];
+    cert_contain_fwd(P, ChainResult{g.d_hit, g.d_stop, g.wall != 0u}, coarse_anchor(P, t, 0u), p);
+  }
+  if (P.use_rc && p < P.num_kmers && P.R[p] == kDeep) {
+    const uint32_t t = p / P.gsize;
+    const CoarseGroup g = groups[2u * t + 1u];
+    cert_contain_rc(P, ChainResult{g.d_hit, g.d_stop, g.wall != 0u}, coarse_anchor(P, t, 1u), p);
   }
 }
 

@@ -351,78 +351,23 @@ __global__ void __launch_bounds__(64, 16) k_free_cert(DevIndex ix, SegParams P, 
   flush_counter(&P.counters[CTR_SEEDS], seeds);
 }
 
-// coarse round before pass 2 (free_cert_coarse_group) as three small kernels, so that the few long chains do not hold
-// thread slots the first pass of other segments (other streams) could use:
-//   scan   one warp per (group of P.gsize positions, strand): outermost / innermost deep entry -> CoarseGroup, and
-//          the groups that have any are appended to a list;
-//   chain  one thread per listed group: the one chain (blocks of 32 threads);
-//   settle one warp per listed group: the containment rule for every deep entry of the group.
-__global__ void __launch_bounds__(kBlock) k_coarse_scan(SegParams P, uint32_t ngroups, CoarseGroup *groups, uint32_t *list,
-                                                        uint32_t *count) {
-  constexpr unsigned kFull = 0xFFFFFFFFu;
-  const uint32_t lane = threadIdx.x & 31u;
-  const uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const uint32_t t = w >> 1, part = w & 1u, gs = P.gsize;
-  if (t >= ngroups || (part && !P.use_rc)) return;
-  uint32_t lo = kNoBarrier, hi = 0;
-  if (part == 0u) {
-    const uint32_t first = t * gs + 1;
-    uint32_t last = first + gs - 1;
-    if (last > P.seg_len) last = P.seg_len;
-    for (uint32_t e = first + lane; e <= last; e += 32u)
-      if (P.G[e] == kDeep) { if (lo == kNoBarrier) lo = e; hi = e; }
-  } else {
-    const uint32_t first = t * gs;
-    uint32_t end = first + gs;
-    if (end > P.num_kmers) end = P.num_kmers;
-    for (uint32_t i = first + lane; i < end; i += 32u)
-      if (P.R[i] == kDeep) { if (lo == kNoBarrier) lo = i; hi = i; }
-  }
-  lo = __reduce_min_sync(kFull, lo);
-  hi = __reduce_max_sync(kFull, hi);
-  if (lane == 0u && lo != kNoBarrier) {
-    groups[w].lo = lo;
-    groups[w].hi = hi;
-    list[atomicAdd(count, 1u)] = w;
-  }
-}
-
-__global__ void __launch_bounds__(32) k_coarse_chain(DevIndex ix, SegParams P, CoarseGroup *groups, const uint32_t *list,
-                                                     const uint32_t *count) {
+// coarse round (coarse_anchor_thread / coarse_settle_thread, nm_core.cuh): the anchor chains run on the workspace's
+// second stream beside the first pass (blocks of 32 threads: the few long chains hold few thread slots), the settle
+// kernel after both
+__global__ void __launch_bounds__(32) k_coarse_anchor(DevIndex ix, SegParams P, uint32_t ngroups, CoarseGroup *groups) {
   __shared__ uint32_t sC[8];
   const uint32_t *C32 = stage_c32(ix, sC);
+  // a warp = 32 consecutive groups of one strand, like k_free_cert
   const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t warp = j >> 5, t = (warp >> 1) * 32u + (j & 31u), part = warp & 1u;
   uint32_t steps = 0, seeds = 0;
-  if (j < *count) {
-    const uint32_t w = list[j];
-    CoarseGroup g = groups[w];
-    // forward strand: from the LARGEST deep end; other strand: from the SMALLEST deep start
-    // (one call for both kinds: the lanes of a warp hold chains of either kind and must stay converged)
-    const ChainResult r = run_chain(ix, C32, P, w & 1u, (w & 1u) ? g.lo : g.hi, P.kmax + (g.hi - g.lo), steps, seeds);
-    g.d_hit = r.d_hit;
-    g.d_stop = r.d_stop;
-    g.wall = r.wall ? 1u : 0u;
-    groups[w] = g;
-  }
+  if (t < ngroups && (part == 0u || P.use_rc)) groups[2u * t + part] = coarse_anchor_thread(ix, C32, P, t, part, steps, seeds);
   flush_counter(&P.counters[CTR_LF], steps);
   flush_counter(&P.counters[CTR_SEEDS], seeds);
 }
-
-__global__ void __launch_bounds__(kBlock) k_coarse_settle(SegParams P, const CoarseGroup *groups, const uint32_t *list,
-                                                          const uint32_t *count) {
-  const uint32_t lane = threadIdx.x & 31u;
-  const uint32_t j = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  if (j >= *count) return;
-  const uint32_t w = list[j];
-  const CoarseGroup g = groups[w];
-  const ChainResult r{g.d_hit, g.d_stop, g.wall != 0u};
-  if ((w & 1u) == 0u) {
-    for (uint32_t e = g.lo + lane; e <= g.hi; e += 32u)
-      if (P.G[e] == kDeep) cert_contain_fwd(P, r, g.hi, e);
-  } else {
-    for (uint32_t i = g.lo + lane; i <= g.hi; i += 32u)
-      if (P.R[i] == kDeep) cert_contain_rc(P, r, g.lo, i);
-  }
+__global__ void __launch_bounds__(kBlock) k_coarse_settle(SegParams P, const CoarseGroup *groups) {
+  const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p <= P.seg_len) coarse_settle_thread(P, groups, p);
 }
 
 __global__ void __launch_bounds__(kBlock) k_free_generic(DevIndex ix, SegParams P, bool all) {
@@ -533,14 +478,12 @@ void launch_free_cert(const DevIndex &ix, const SegParams &P, cudaStream_t st) {
   const uint32_t ngroups = (uint32_t)(((uint64_t)P.seg_len + 1 + P.gsize - 1) / P.gsize);
   k_free_cert<<<grid_for(2ull * (((uint64_t)ngroups + 31) / 32 * 32), 64), 64, 0, st>>>(ix, P, ngroups);
 }
-void launch_free_cert_coarse(const DevIndex &ix, const SegParams &P, CoarseGroup *groups, uint32_t *list, uint32_t *count,
-                             cudaStream_t st) {
+void launch_coarse_anchor(const DevIndex &ix, const SegParams &P, CoarseGroup *groups, cudaStream_t st) {
   const uint32_t ngroups = (uint32_t)(((uint64_t)P.seg_len + 1 + P.gsize - 1) / P.gsize);
-  cudaMemsetAsync(count, 0, 4, st);
-  k_coarse_scan<<<grid_for(64ull * ngroups), kBlock, 0, st>>>(P, ngroups, groups, list, count);
-  // the number of listed groups stays on the device: both kernels are launched for the most there can be
-  k_coarse_chain<<<grid_for(2ull * ngroups, 32), 32, 0, st>>>(ix, P, groups, list, count);
-  k_coarse_settle<<<grid_for(64ull * ngroups), kBlock, 0, st>>>(P, groups, list, count);
+  k_coarse_anchor<<<grid_for(2ull * (((uint64_t)ngroups + 31) / 32 * 32), 32), 32, 0, st>>>(ix, P, ngroups, groups);
+}
+void launch_coarse_settle(const SegParams &P, const CoarseGroup *groups, cudaStream_t st) {
+  k_coarse_settle<<<grid_for((uint64_t)P.seg_len + 1), kBlock, 0, st>>>(P, groups);
 }
 void launch_free_generic(const DevIndex &ix, const SegParams &P, bool all, cudaStream_t st) {
   k_free_generic<<<grid_for((uint64_t)P.seg_len + 1), kBlock, 0, st>>>(ix, P, all);

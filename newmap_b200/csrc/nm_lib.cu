@@ -74,8 +74,9 @@ struct nm_workspace {
   uint32_t opt_ref_lf = 0, opt_dcap = 0, opt_gsize = 0, opt_pass1 = 0, opt_gsize2 = ~0u, opt_own_chains = ~0u, opt_stall = ~0u;
   // several sequences x several indexes (nm_workspace_multi); cleared by the next upload / attach
   nm::CoarseGroup *d_cgroups = nullptr;  // coarse certificate round: 2 per group of >= kMinGsize2 positions
-  uint32_t *d_clist = nullptr;           // listed groups; [cap] = their number
   uint64_t cgroup_cap = 0;
+  cudaStream_t aux_stream = nullptr;     // the coarse round's anchor chains run here, beside the first pass
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   nm::MultiSet *d_multi = nullptr;
   uint8_t *d_extra[nm::kMaxMulti]{};  // extra sequences' segments, max_seg_len + 16 bytes each, allocated on demand
   uint32_t multi_ix = 0, multi_seq = 0;
@@ -285,7 +286,9 @@ int ws_alloc(nm_workspace *ws) {
   NM_CUDA(cudaMalloc(&ws->d_out, (n + 1) * 4));
   ws->cgroup_cap = 2 * ((n + 1) / kMinGsize2 + 2);
   NM_CUDA(cudaMalloc((void **)&ws->d_cgroups, ws->cgroup_cap * sizeof(nm::CoarseGroup)));
-  NM_CUDA(cudaMalloc((void **)&ws->d_clist, (ws->cgroup_cap + 1) * 4));
+  NM_CUDA(cudaStreamCreateWithFlags(&ws->aux_stream, cudaStreamNonBlocking));
+  NM_CUDA(cudaEventCreateWithFlags(&ws->ev_fork, cudaEventDisableTiming));
+  NM_CUDA(cudaEventCreateWithFlags(&ws->ev_join, cudaEventDisableTiming));
   NM_CUDA(cudaMalloc((void **)&ws->d_counters, nm::CTR_N * 8));
   NM_CUDA(cudaHostAlloc((void **)&ws->h_counters, nm::CTR_N * 8, cudaHostAllocDefault));
   for (auto &e : ws->ev) NM_CUDA(cudaEventCreate(&e));
@@ -318,6 +321,22 @@ int run_search(nm_workspace *ws, int algo) {
     const bool fast = (algo != NM_ALGO_FREE_GENERIC) && ix->has_rank32 && P.kmin >= ix->dev.seed_len;
     P.fast = fast ? 1 : 0;
     const bool deep_passes = fast && P.dcap < P.kmax;
+    // coarse round (coarse_anchor_thread, nm_core.cuh): anchor chains of max_k + gsize2 - 1 steps at fixed positions,
+    // on the workspace's second stream BESIDE the first pass, settled after both.  Off by default: it removes a third
+    // of a segment's LF steps (2.8 -> 2.0 per position on the 1 Gbp bench genome), but beside the first pass, which
+    // keeps the memory system at its random-access ceiling, a dependent step costs about 3 us and the 455-step chains
+    // end 0.6 ms after it (8.73 -> 8.12 G positions/s); run alone after it they take 0.7 ms (profiles/r1_gsize2_*).
+    const uint32_t g2 = ws->opt_gsize2 == ~0u ? 0u : ws->opt_gsize2;
+    const bool coarse = deep_passes && g2 > P.gsize && g2 >= kMinGsize2;
+    nm::SegParams Pc = P;
+    if (coarse) {
+      Pc.gsize = g2;
+      NM_CUDA(cudaEventRecord(ws->ev_fork, st));
+      NM_CUDA(cudaStreamWaitEvent(ws->aux_stream, ws->ev_fork, 0));
+      nm::launch_coarse_anchor(ix->dev, Pc, ws->d_cgroups, ws->aux_stream);
+      NM_CUDA(cudaEventRecord(ws->ev_join, ws->aux_stream));
+      ++ws->launches;
+    }
     if (fast) {
       // tiled kernel when the chains are short (deep seed table); with the file's 12-letter table the chains run
       // 4-5 steps on average and one thread per position is faster (measured: profiles/r1_seed_depth_sweep.md)
@@ -328,19 +347,10 @@ int run_search(nm_workspace *ws, int algo) {
     }
     NM_CUDA(cudaEventRecord(ws->ev[EV_PASS1], st));
     if (deep_passes) {
-      // coarse round first: one chain per `gsize2` positions and strand, run that much deeper, settles the inside of long exact
-      // repeats (tandem arrays, recent duplications) where every group of the fine round would otherwise pay a chain
-      // of max_k steps; what it cannot settle stays deep for the fine round
-      // Off by default: it removes a third of the LF steps of a segment (3.1 -> 2.1 per position on the 1 Gbp bench
-      // genome) but its chains are max_k + gsize2 DEPENDENT steps at about 1.5 us each, longer than everything it saves
-      // when the kernels of a segment run one after the other (profiles/r1_gsize2_sweep_c3_1g.jsonl).
-      const uint32_t g2 = ws->opt_gsize2 == ~0u ? 0u : ws->opt_gsize2;
-      if (g2 > P.gsize && g2 >= kMinGsize2) {
-        nm::SegParams Pc = P;
-        Pc.gsize = g2;
-        Pc.own_chains = 0;
-        nm::launch_free_cert_coarse(ix->dev, Pc, ws->d_cgroups, ws->d_clist, ws->d_clist + ws->cgroup_cap, st);
-        ws->launches += 3;
+      if (coarse) {
+        NM_CUDA(cudaStreamWaitEvent(st, ws->ev_join, 0));
+        nm::launch_coarse_settle(Pc, ws->d_cgroups, st);
+        ++ws->launches;
       }
       nm::launch_free_cert(ix->dev, P, st);
       ++ws->launches;
@@ -521,7 +531,9 @@ void nm_workspace_destroy(nm_workspace *ws) {
   cudaFree(ws->d_klist);
   cudaFree(ws->d_multi);
   cudaFree(ws->d_cgroups);
-  cudaFree(ws->d_clist);
+  if (ws->aux_stream) cudaStreamDestroy(ws->aux_stream);
+  if (ws->ev_fork) cudaEventDestroy(ws->ev_fork);
+  if (ws->ev_join) cudaEventDestroy(ws->ev_join);
   for (auto *p : ws->d_extra) cudaFree(p);
   cudaFree(ws->d_counters);
   if (ws->h_counters) cudaFreeHost(ws->h_counters);

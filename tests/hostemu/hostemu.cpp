@@ -139,13 +139,15 @@ int emu_min_unique(EmuIndex *ix, const uint8_t *seg, uint32_t seg_len, uint32_t 
       for (uint32_t p = 0; p <= seg_len; ++p) free_chain_thread(ix->dev, ix->c32, P, p, true, steps, seeds);
       if (P.dcap < P.kmax) {
         uint32_t s2 = 0;
-        if (gsize2 > P.gsize) {  // nm_lib.cu run_search: coarse round first, containment and interpolation only
+        if (gsize2 > P.gsize) {  // nm_lib.cu run_search: coarse round (anchor chains at fixed positions, containment only)
           SegParams Pc = P;
           Pc.gsize = gsize2;
-          Pc.own_chains = 0;
           const uint32_t nc = (seg_len + 1 + Pc.gsize - 1) / Pc.gsize;
+          std::vector<CoarseGroup> groups(2 * (size_t)nc);
           for (uint32_t t = 0; t < nc; ++t)
-            for (uint32_t part = 0; part < 2; ++part) free_cert_coarse_group(ix->dev, ix->c32, Pc, t, part, s2, seeds);
+            for (uint32_t part = 0; part < 2; ++part)
+              if (part == 0 || P.use_rc) groups[2 * t + part] = coarse_anchor_thread(ix->dev, ix->c32, Pc, t, part, s2, seeds);
+          for (uint32_t p = 0; p <= seg_len; ++p) coarse_settle_thread(Pc, groups.data(), p);
         }
         const uint32_t ngroups = (seg_len + 1 + P.gsize - 1) / P.gsize;
         for (uint32_t t = 0; t < ngroups; ++t) free_cert_thread(ix->dev, ix->c32, P, t, s2, seeds);

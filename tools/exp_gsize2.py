@@ -28,9 +28,12 @@ want = None
 PAIRS = ((16, 0), (16, 64), (16, 128), (16, 256), (16, 512), (16, 1024), (32, 256), (32, 512), (8, 128), (8, 256))
 if len(sys.argv) > 4:      # "16:0,24:0,32:0"
     PAIRS = tuple(tuple(int(x) for x in pr.split(":")) for pr in sys.argv[4].split(","))
-for gsize, gsize2 in PAIRS:
+for pair in PAIRS:
+    gsize, gsize2 = pair[0], pair[1]
+    dcap = pair[2] if len(pair) > 2 else 0      # "gsize:gsize2:dcap"
     ws.option("gsize", gsize)
     ws.option("gsize2", gsize2)
+    ws.option("dcap", dcap)
     tot = {}
     sums = []
     for (seg, n), pb in zip(segs, pbs):
@@ -45,6 +48,6 @@ for gsize, gsize2 in PAIRS:
         for k in ("ms_search", "ms_pass1", "ms_cert", "ms_pass3", "lf_steps", "lf_steps_pass1"):
             tot[k] = tot.get(k, 0) + best[k]
     want = want or sums
-    row = {"gsize": gsize, "gsize2": gsize2, "same": sums == want, "segments": len(segs)}
+    row = {"gsize": gsize, "gsize2": gsize2, "dcap": dcap, "same": sums == want, "segments": len(segs)}
     row.update({k: (round(v / len(segs), 4) if isinstance(v, float) else v // len(segs)) for k, v in tot.items()})
     print(json.dumps(row), flush=True)

@@ -29,7 +29,7 @@ constexpr uint32_t kFaTile = 4096;          // bytes per compaction tile (one bl
 constexpr uint32_t kFaThreads = 256;
 constexpr uint32_t kFaPerThread = kFaTile / kFaThreads;
 constexpr uint64_t kMaxHeaders = 1ull << 22;
-constexpr uint64_t kStageBytes = 8ull << 20;   // pinned staging chunk (two per reader thread)
+constexpr uint64_t kStageBytes = 2ull << 20;   // pinned staging chunk (two per reader thread; pinning costs time per byte)
 
 int fa_fail(cudaError_t e, const char *what) {
   nm_internal_set_cuda_error(what, cudaGetErrorString(e));

@@ -39,6 +39,8 @@ ALLOWED_BASES = b"ACGTactg"          # sic (search.py:23): the set is right, the
 UNIQUE_COUNT_FILENAME_FORMAT = "{}.unique.{}"
 PIPELINE_DEPTH = int(os.environ.get("NEWMAP_B200_PIPELINE", "3"))
 DEVICE_PIPELINE_DEPTH = int(os.environ.get("NEWMAP_B200_DEVICE_PIPELINE", "4"))
+WRITER_THREADS = int(os.environ.get("NEWMAP_B200_WRITERS", "8"))   # threads writing <id>.unique.uintN windows (pwrite)
+READER_THREADS = int(os.environ.get("NEWMAP_B200_READERS", "0"))   # threads reading the FASTA text into pinned staging (0 = library default)
 # "device": the FASTA text is parsed on the GPU (nm_fasta_*) and segments are searched where they lie;
 # "host": newmap_b200/fasta.py cuts the segments and every segment is uploaded.  Default: device unless --verbose
 # (the per-sequence statistics of the verbose log need the segment bytes on the host).
@@ -500,7 +502,7 @@ def _write_unique_counts_device(config: SearchConfig, ix: _lib.Index, data_type,
     # workspaces and pinned output buffers are allocated while the file is being read
     maker = ThreadPoolExecutor(max_workers=1)
     made = maker.submit(lambda: [_DeviceSlot(ix, requested_sequence_length, itemsize)
-                                 for _ in range(DEVICE_PIPELINE_DEPTH + 2)])
+                                 for _ in range(DEVICE_PIPELINE_DEPTH + max(2, WRITER_THREADS - 1))])
     try:
         if path.suffix == ".gz":
             with optional_gzip_open(path, "rb") as fh:
@@ -510,7 +512,7 @@ def _write_unique_counts_device(config: SearchConfig, ix: _lib.Index, data_type,
                         break
                     fa.feed(block)
         else:
-            fa.feed_file(path)
+            fa.feed_file(path, READER_THREADS)
         mark("text_on_device")
         try:
             fa.finish()
@@ -546,7 +548,7 @@ def _write_unique_counts_device(config: SearchConfig, ix: _lib.Index, data_type,
                                        (offset + num_kmers) * itemsize if epilogue else None)
             slot.job = None
 
-        with ThreadPoolExecutor(max_workers=3) as pool:
+        with ThreadPoolExecutor(max_workers=max(1, WRITER_THREADS)) as pool:
             try:
                 for header, rec_off, rec_len in fa.records:
                     tokens = header.split()

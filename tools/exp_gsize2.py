@@ -34,6 +34,8 @@ for pair in PAIRS:
     ws.option("gsize", gsize)
     ws.option("gsize2", gsize2)
     ws.option("dcap", dcap)
+    own = pair[3] if len(pair) > 3 else 1        # "gsize:gsize2:dcap:own_chains"
+    ws.option("own_chains", own)
     tot = {}
     sums = []
     for (seg, n), pb in zip(segs, pbs):
@@ -48,6 +50,6 @@ for pair in PAIRS:
         for k in ("ms_search", "ms_pass1", "ms_cert", "ms_pass3", "lf_steps", "lf_steps_pass1"):
             tot[k] = tot.get(k, 0) + best[k]
     want = want or sums
-    row = {"gsize": gsize, "gsize2": gsize2, "dcap": dcap, "same": sums == want, "segments": len(segs)}
+    row = {"gsize": gsize, "gsize2": gsize2, "dcap": dcap, "own_chains": own, "same": sums == want, "segments": len(segs)}
     row.update({k: (round(v / len(segs), 4) if isinstance(v, float) else v // len(segs)) for k, v in tot.items()})
     print(json.dumps(row), flush=True)

@@ -152,6 +152,8 @@ int nm_workspace_sync(nm_workspace *ws, nm_stats *stats);
                              goes to the third pass); default 1 */
 #define NM_OPT_STALL 7    /* first pass: a chain whose interval kept its size for this many steps in a row is left to the
                              later passes at once instead of at the depth cap (it is inside a repeat); default 0 = off */
+#define NM_OPT_CERT_RUNS 8 /* certificate pass: runs of consecutive unsettled positions a thread takes per group and strand
+                             (one anchor chain each; the rest goes to the third pass); 0 = default 4 */
 int nm_workspace_option(nm_workspace *ws, int option, uint64_t value);
 /* 64-bit FNV-style checksum of the last search's output computed on the device (for
  * device-resident runs that never copy the output back). */

@@ -288,8 +288,8 @@ class Workspace:
             pass
 
     def option(self, name: str, value: int):
-        """'ref_lf' | 'dcap' | 'gsize' | 'pass1' | 'gsize2' | 'own_chains' | 'stall' (NM_OPT_*): instrumentation / tuning, never changes results."""
-        check(load().nm_workspace_option(self._h, {"ref_lf": 1, "dcap": 2, "gsize": 3, "pass1": 4, "gsize2": 5, "own_chains": 6, "stall": 7}[name], int(value)),
+        """'ref_lf' | 'dcap' | 'gsize' | 'pass1' | 'gsize2' | 'own_chains' | 'stall' | 'cert_runs' (NM_OPT_*): instrumentation / tuning, never changes results."""
+        check(load().nm_workspace_option(self._h, {"ref_lf": 1, "dcap": 2, "gsize": 3, "pass1": 4, "gsize2": 5, "own_chains": 6, "stall": 7, "cert_runs": 8}[name], int(value)),
               "nm_workspace_option")
 
     def attach(self, fasta: "Fasta", seq_offset: int, seg_len: int):

@@ -359,6 +359,7 @@ struct SegParams {
   uint32_t dcap;   // first-pass depth cap of the trajectory-free search (characters, > seed_len)
   uint32_t gsize;  // positions per certificate group of the deep pass
   uint32_t own_chains;  // chains of their own a certificate thread may run for positions no bound settles
+  uint32_t cert_runs;   // certificate pass: runs of consecutive deep entries a thread takes per group and strand
   uint32_t stall;       // first pass: a chain whose interval kept its size for this many steps in a row is left deep (0 = off)
 };
 
@@ -787,81 +788,113 @@ NM_HD bool cert_contain_rc(const SegParams &P, const ChainResult &r, uint32_t i0
 // pass 2: group t covers ends e in (t*gs, (t+1)*gs] and starts i in [t*gs, (t+1)*gs)
 // (parts: bit 0 = the forward-strand half, bit 1 = the other-strand half; the kernel gives each half its own thread
 // so that the two long chains of a group run side by side)
+//
+// One run [a, b] of consecutive deep ends, forward strand: ONE chain from its LARGEST end b, run (b - a) deeper than
+// max_k; it contains seg[e-L, e) for every smaller e of the run.
+NM_HD void cert_run_fwd(const DevIndex &ix, const uint32_t *C32, const SegParams &P, uint32_t a, uint32_t b, uint32_t &budget,
+                        uint32_t &steps, uint32_t &seeds) {
+  const ChainResult r = run_fwd_chain(ix, C32, P, b, P.kmax + (b - a), steps, seeds);
+  // nu: the deepest explored length at which seg[b-nu, b) still occurs at least twice
+  const uint32_t nu = r.d_hit ? r.d_hit - 1u : r.d_stop;
+  uint32_t e = a;
+  for (;;) {
+    // settle ends from the left until one needs a chain of its own.  (That chain is run AFTER this loop: the lanes of a
+    // warp meet such an end in different iterations, and a chain inside the loop would run for one lane at a time.)
+    uint32_t need = 0;
+    for (; e <= b; ++e) {
+      if (P.G[e] != kDeep) continue;
+      const uint32_t dt = b - e;
+      if (cert_contain_fwd(P, r, b, e)) continue;
+      const bool beyond_wall = r.wall && r.d_stop <= dt;  // e lies beyond the wall b's chain ran into
+      // seg[e-l, e) lies inside seg[b-nu, b) for l <= nu - dt, so G[e] >= nu - dt + 1; and a unique suffix of
+      // length g ending at e-1 makes the suffix of length g+1 ending at e unique, so G[e] <= G[e-1] + 1.  Where the
+      // two bounds meet (a run of positions since the last difference between two copies of a repeat: G grows by
+      // one per position) the value is settled without a chain of its own.
+      // (e-1 may belong to the group on the left, whose thread may be writing it right now: what is read is either
+      // kDeep or a final value, both are safe; only the number of chains run depends on the timing)
+      if (!beyond_wall && nu >= dt) {
+        const uint32_t left = P.G[e - 1];
+        if (left != kNone && left != kDeep && left != kPending && left + 1u == nu - dt + 1u) {
+          P.G[e] = left + 1u;
+          continue;
+        }
+      }
+      if (!need) need = e;                           // the first such end gets a chain (if the budget allows) ...
+      if (budget) break;                             // ... and the ends after it may then interpolate from its value
+    }
+    if (!need || !budget) break;                     // (without budget the loop above ran to the end: the rest stays deep)
+    --budget;
+    P.G[need] = chain_value(P, run_fwd_chain(ix, C32, P, need, P.kmax, steps, seeds), P.kmax, kNone);
+    e = need + 1;
+  }
+}
+// mirror image, other strand: ONE chain from the SMALLEST start a of the run; it contains seg[i, i+L) for every larger i
+NM_HD void cert_run_rc(const DevIndex &ix, const uint32_t *C32, const SegParams &P, uint32_t a, uint32_t b, uint32_t &budget,
+                       uint32_t &steps, uint32_t &seeds) {
+  const ChainResult r = run_rc_chain(ix, C32, P, a, P.kmax + (b - a), steps, seeds);
+  const uint32_t nu = r.d_hit ? r.d_hit - 1u : r.d_stop;  // rc(seg[a, a+nu)) still occurs
+  uint32_t n = b - a + 1u;                           // starts a .. a+n-1 still to look at, from the right: R[i] <= R[i+1] + 1
+  for (;;) {
+    uint32_t need = kNoBarrier;
+    for (; n > 0u; --n) {
+      const uint32_t i = a + n - 1u;
+      if (P.R[i] != kDeep) continue;
+      const uint32_t dt = i - a;
+      if (cert_contain_rc(P, r, a, i)) continue;
+      const bool beyond_wall = r.wall && r.d_stop <= dt;
+      if (!beyond_wall && nu >= dt && i + 1 < P.seg_len) {
+        const uint32_t right = P.R[i + 1];
+        if (right != kInf && right != kDeep && right != kPending && right + 1u == nu - dt + 1u) {
+          P.R[i] = right + 1u;
+          continue;
+        }
+      }
+      if (need == kNoBarrier) need = i;
+      if (budget) break;
+    }
+    if (need == kNoBarrier || !budget) break;
+    --budget;
+    P.R[need] = chain_value(P, run_rc_chain(ix, C32, P, need, P.kmax, steps, seeds), P.kmax, kInf);
+    n = need - a;                                    // continue with the starts to the left of it
+  }
+}
+
+// A group's deep entries fall into runs of consecutive positions: inside one repeat copy the runs are separated by
+// the dcap positions after each difference between the copies (those were settled by the first pass), so a group no
+// wider than dcap holds one run and a wider one holds a few.  Each run gets its own anchor chain; at most kCertRuns
+// runs per group and strand are taken, the rest stays deep for the third pass.
+constexpr uint32_t kCertRuns = 4;  // default of P.cert_runs
 NM_HD void free_cert_thread(const DevIndex &ix, const uint32_t *C32, const SegParams &P, uint32_t t, uint32_t &steps,
                             uint32_t &seeds, uint32_t parts = 3u) {
   const uint32_t gs = P.gsize;
-  // ---- forward strand: chain from the LARGEST deep end e0; it contains seg[e'-L, e') for every smaller e'
-  if (parts & 1u) {
+  if (parts & 1u) {  // ---- forward strand
     const uint32_t first = t * gs + 1;
     uint32_t last = first + gs - 1;
     if (last > P.seg_len) last = P.seg_len;
-    uint32_t e0 = 0, emin = 0;
-    for (uint32_t e = first; e <= last; ++e)
-      if (P.G[e] == kDeep) { e0 = e; if (!emin) emin = e; }
-    if (e0) {
-      const ChainResult r = run_fwd_chain(ix, C32, P, e0, P.kmax + (e0 - emin), steps, seeds);
-      // nu: the deepest explored length at which seg[e0-nu, e0) still occurs at least twice (e0 was kDeep, so the
-      // chain got beyond the first pass's cap before it could hit)
-      const uint32_t nu = r.d_hit ? r.d_hit - 1u : r.d_stop;
-      uint32_t budget = P.own_chains;
-      for (uint32_t e = emin; e <= e0; ++e) {
-        if (P.G[e] != kDeep) continue;
-        const uint32_t dt = e0 - e;
-        if (cert_contain_fwd(P, r, e0, e)) continue;
-        const bool beyond_wall = r.wall && r.d_stop <= dt;  // e lies beyond the wall e0's chain ran into
-        // seg[e-l, e) lies inside seg[e0-nu, e0) for l <= nu - dt, so G[e] >= nu - dt + 1; and a unique suffix of
-        // length g ending at e-1 makes the suffix of length g+1 ending at e unique, so G[e] <= G[e-1] + 1.  Where the
-        // two bounds meet (a run of positions since the last difference between two copies of a repeat: G grows by
-        // one per position) the value is settled without a chain of its own.
-        // (e-1 may belong to the group on the left, whose thread may be writing it right now: what is read is either
-        // kDeep or a final value, both are safe; only the number of chains run depends on the timing)
-        if (!beyond_wall && nu >= dt) {
-          const uint32_t left = P.G[e - 1];
-          if (left != kNone && left != kDeep && left != kPending && left + 1u == nu - dt + 1u) {
-            P.G[e] = left + 1u;
-            continue;
-          }
-        }
-        if (budget) {                                    // else: left kDeep for the third pass
-          --budget;
-          P.G[e] = chain_value(P, run_fwd_chain(ix, C32, P, e, P.kmax, steps, seeds), P.kmax, kNone);
-        }
-      }
+    // (the r-th runs of the lanes of a warp are taken in the same iteration of this loop, so their chains run side by
+    // side; with the chain inside the scanning loop each lane would reach it in another iteration, one after the other)
+    uint32_t budget = P.own_chains, e = first;
+    for (uint32_t r = 0; r < P.cert_runs; ++r) {
+      while (e <= last && P.G[e] != kDeep) ++e;
+      if (e > last) break;
+      uint32_t b = e;
+      while (b < last && P.G[b + 1] == kDeep) ++b;
+      cert_run_fwd(ix, C32, P, e, b, budget, steps, seeds);
+      e = b + 1;
     }
   }
-  // ---- other strand: chain from the SMALLEST deep start i0; it contains seg[i', i'+L) for every larger i'
-  if (P.use_rc && (parts & 2u)) {
+  if (P.use_rc && (parts & 2u)) {  // ---- other strand
     const uint32_t first = t * gs;
     uint32_t end = first + gs;
     if (end > P.num_kmers) end = P.num_kmers;
-    uint32_t i0 = kNoBarrier, imax = 0;
-    for (uint32_t i = first; i < end; ++i)
-      if (P.R[i] == kDeep) { if (i0 == kNoBarrier) i0 = i; imax = i; }
-    if (i0 != kNoBarrier) {
-      const ChainResult r = run_rc_chain(ix, C32, P, i0, P.kmax + (imax - i0), steps, seeds);
-      const uint32_t nu = r.d_hit ? r.d_hit - 1u : r.d_stop;  // rc(seg[i0, i0+nu)) still occurs
-      uint32_t budget = P.own_chains;
-      for (uint32_t i = imax;; --i) {                    // right to left: R[i] <= R[i+1] + 1
-        if (P.R[i] == kDeep) {
-          const uint32_t dt = i - i0;
-          const bool beyond_wall = r.wall && r.d_stop <= dt;
-          if (!cert_contain_rc(P, r, i0, i)) {
-            bool done = false;
-            if (!beyond_wall && nu >= dt && i + 1 < P.seg_len) {
-              const uint32_t right = P.R[i + 1];
-              if (right != kInf && right != kDeep && right != kPending && right + 1u == nu - dt + 1u) {
-                P.R[i] = right + 1u;
-                done = true;
-              }
-            }
-            if (!done && budget) {
-              --budget;
-              P.R[i] = chain_value(P, run_rc_chain(ix, C32, P, i, P.kmax, steps, seeds), P.kmax, kInf);
-            }
-          }
-        }
-        if (i == i0) break;
-      }
+    uint32_t budget = P.own_chains, i = first;
+    for (uint32_t r = 0; r < P.cert_runs; ++r) {
+      while (i < end && P.R[i] != kDeep) ++i;
+      if (i >= end) break;
+      uint32_t b = i;
+      while (b + 1 < end && P.R[b + 1] == kDeep) ++b;
+      cert_run_rc(ix, C32, P, i, b, budget, steps, seeds);
+      i = b + 1;
     }
   }
 }

@@ -71,7 +71,7 @@ struct nm_workspace {
   int algo_req = 0, algo_used = 0;
   bool timed_h2d = false, timed_d2h = false;
   void *pending_out = nullptr;
-  uint32_t opt_ref_lf = 0, opt_dcap = 0, opt_gsize = 0, opt_pass1 = 0, opt_gsize2 = ~0u, opt_own_chains = ~0u, opt_stall = ~0u;
+  uint32_t opt_ref_lf = 0, opt_dcap = 0, opt_gsize = 0, opt_pass1 = 0, opt_gsize2 = ~0u, opt_own_chains = ~0u, opt_stall = ~0u, opt_cert_runs = 0;
   // several sequences x several indexes (nm_workspace_multi); cleared by the next upload / attach
   nm::CoarseGroup *d_cgroups = nullptr;  // coarse certificate round: 2 per group of >= kMinGsize2 positions
   uint64_t cgroup_cap = 0;
@@ -680,6 +680,7 @@ int nm_workspace_search(nm_workspace *ws, uint64_t num_kmers, int mode, const ui
     if (P.dcap <= sl) P.dcap = sl + 1;
     P.gsize = ws->opt_gsize ? ws->opt_gsize : 20;  // profiles/r1_gsize_sweep_final_c3_1g.jsonl
     P.own_chains = ws->opt_own_chains == ~0u ? nm::kCertOwnChains : ws->opt_own_chains;
+    P.cert_runs = ws->opt_cert_runs ? ws->opt_cert_runs : nm::kCertRuns;
     // only when passes 2 and 3 will run (run_search: deep_passes).  Off by default: with 2 it removes 45 % of the first
     // pass's LF steps on the 1 Gbp bench genome, but those are the cheap ones (neighbouring positions inside a repeat
     // walk the same rank blocks, L2 hits) and the later passes pay more than it saves (8.45 -> 8.03 G positions/s).
@@ -792,6 +793,7 @@ int nm_workspace_option(nm_workspace *ws, int option, uint64_t value) {
     case NM_OPT_GSIZE: if (value > 4096) return NM_EARG; ws->opt_gsize = (uint32_t)value; return NM_OK;
     case NM_OPT_OWN_CHAINS: if (value > 64) return NM_EARG; ws->opt_own_chains = (uint32_t)value; return NM_OK;
     case NM_OPT_STALL: if (value > 64) return NM_EARG; ws->opt_stall = (uint32_t)value; return NM_OK;
+    case NM_OPT_CERT_RUNS: if (value > 64) return NM_EARG; ws->opt_cert_runs = (uint32_t)value; return NM_OK;
     case NM_OPT_GSIZE2: if (value > 65536) return NM_EARG; ws->opt_gsize2 = (uint32_t)value; return NM_OK;
     default: return NM_EARG;
   }

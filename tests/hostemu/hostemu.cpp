@@ -114,6 +114,7 @@ int emu_min_unique(EmuIndex *ix, const uint8_t *seg, uint32_t seg_len, uint32_t 
   P.use_rc = use_rc; P.out_width = out_width;
   P.gsize = gsize ? gsize : 32;
   P.own_chains = kCertOwnChains;
+  P.cert_runs = 1 + (gsize + dcap) % 4;
   if (mode == 0) { P.kmin = klist[0]; P.kmax = klist[1]; }
   else { P.kmin = P.kmax = klist[0]; for (uint32_t j = 0; j < nk; ++j) { if (klist[j] < P.kmin) P.kmin = klist[j]; if (klist[j] > P.kmax) P.kmax = klist[j]; } }
   // nm_lib.cu nm_workspace_search: the deeper table when every queried length reaches its depth (the estimate of the

@@ -317,6 +317,7 @@ def test_tuning_options_do_not_change_results(nm, indexes):
         ws.option("gsize2", (256, 0, 40, 1000)[n % 4])   # coarse certificate round: on, off (default), other sizes
         ws.option("own_chains", (1, 0, 3)[n % 3])
         ws.option("stall", (2, 0, 1, 5, 3)[n % 5])
+        ws.option("cert_runs", (0, 1, 2, 7)[n % 4])
         ws.option("pass1", pass1)     # first-pass kernel: tiled with lane refill / one thread per position
         ws.upload(buf.ptr, len(seq))
         ws.search(len(seq), kl, True, out_width=1)

@@ -36,6 +36,8 @@ for pair in PAIRS:
     ws.option("dcap", dcap)
     own = pair[3] if len(pair) > 3 else 1        # "gsize:gsize2:dcap:own_chains"
     ws.option("own_chains", own)
+    runs = pair[4] if len(pair) > 4 else 0       # "gsize:gsize2:dcap:own_chains:cert_runs"
+    ws.option("cert_runs", runs)
     tot = {}
     sums = []
     for (seg, n), pb in zip(segs, pbs):
@@ -50,6 +52,6 @@ for pair in PAIRS:
         for k in ("ms_search", "ms_pass1", "ms_cert", "ms_pass3", "lf_steps", "lf_steps_pass1"):
             tot[k] = tot.get(k, 0) + best[k]
     want = want or sums
-    row = {"gsize": gsize, "gsize2": gsize2, "dcap": dcap, "own_chains": own, "same": sums == want, "segments": len(segs)}
+    row = {"gsize": gsize, "gsize2": gsize2, "dcap": dcap, "own_chains": own, "cert_runs": runs, "same": sums == want, "segments": len(segs)}
     row.update({k: (round(v / len(segs), 4) if isinstance(v, float) else v // len(segs)) for k, v in tot.items()})
     print(json.dumps(row), flush=True)

@@ -207,7 +207,8 @@ __global__ void __launch_bounds__(kBlock, 8) k_free_chain(DevIndex ix, SegParams
 //   phase B  the lanes pop queued chains and extend them one step per iteration, taking the next chain as soon as
 //            theirs ends, so the warps stay full while the DRAM latency of each step is covered by the other lanes.
 // Same values as free_chain_thread(first = true) (nm_core.cuh) position by position.
-constexpr int kP1Tile = 2 * kBlock;
+constexpr int kP1Win = 2;  // seed windows per thread (3 or 4: shorter kernel when timed alone, slower job: 8.62 -> 7.98 G positions/s)
+constexpr int kP1Tile = kP1Win * kBlock;
 
 __global__ void __launch_bounds__(kBlock, 8) k_pass1_tiled(DevIndex ix, SegParams P) {
   __shared__ uint32_t sC[8];
@@ -222,20 +223,20 @@ __global__ void __launch_bounds__(kBlock, 8) k_pass1_tiled(DevIndex ix, SegParam
   // ---- phase A.  Thread work = two seed windows q (letters q .. q+sl-1); a window seeds the other-strand chain that
   // STARTS at q and the forward-strand chain that ENDS at q + sl, so with the both-strand table one 16-byte entry
   // serves two chains.  Code bytes first, then keys, then entries: the loads of each group are in flight together.
-  SeedEntry32 ent[4];
-  uint32_t st[4];  // 0 outside the segment, 1 not wanted, 2 starts from a letter, 3 starts from the seed table
+  SeedEntry32 ent[2 * kP1Win];
+  uint32_t st[2 * kP1Win];  // 0 outside the segment, 1 not wanted, 2 starts from a letter, 3 starts from the seed table
   {
-    uint32_t cself[2], clast[2];  // codes[q], codes[q + sl - 1]
+    uint32_t cself[kP1Win], clast[kP1Win];  // codes[q], codes[q + sl - 1]
 #pragma unroll
-    for (int j = 0; j < 2; ++j) {
+    for (int j = 0; j < kP1Win; ++j) {
       const uint32_t q = t0 + j * kBlock + threadIdx.x;
       const uint64_t e = (uint64_t)q + P.sl;
       cself[j] = q < P.seg_len ? (uint32_t)ld8(P.codes + q) : (uint32_t)(kNoStart | kSeedBad);
       clast[j] = e <= P.seg_len ? (uint32_t)ld8(P.codes + e - 1) : (uint32_t)kBarrier;
     }
-    uint32_t key[2];
+    uint32_t key[kP1Win];
 #pragma unroll
-    for (int j = 0; j < 2; ++j) {
+    for (int j = 0; j < kP1Win; ++j) {
       const uint32_t q = t0 + j * kBlock + threadIdx.x;
       const uint64_t e = (uint64_t)q + P.sl;
       const bool window_ok = !(cself[j] & kSeedBad);
@@ -249,7 +250,7 @@ __global__ void __launch_bounds__(kBlock, 8) k_pass1_tiled(DevIndex ix, SegParam
       key[j] = (v0 == 3u || v1 == 3u) ? ld32(P.seedkey + q) : 0u;
     }
 #pragma unroll
-    for (int j = 0; j < 2; ++j) {
+    for (int j = 0; j < kP1Win; ++j) {
       ent[2 * j] = ent[2 * j + 1] = SeedEntry32{0u, 0u};
       if (st[2 * j] == 3u || st[2 * j + 1] == 3u) {
         if (P.seedpair) {
@@ -273,7 +274,7 @@ __global__ void __launch_bounds__(kBlock, 8) k_pass1_tiled(DevIndex ix, SegParam
     }
   }
 #pragma unroll
-  for (int slot = 0; slot < 4; ++slot) {
+  for (int slot = 0; slot < 2 * kP1Win; ++slot) {
     const uint32_t kind = slot & 1;
     const uint32_t p = t0 + (slot >> 1) * kBlock + threadIdx.x + (kind == 0u ? P.sl : 0u);
     if (st[slot] == 0) continue;

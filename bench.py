@@ -418,16 +418,6 @@ def main():
         positions_all = float(positions_per_step)
 
     if rank == 0:
-        # kernel durations: the CUDA events the library records around every kernel, taken from the TIMED region of the
-        # device-resident arm when that arm runs on one stream (kernels strictly one after the other, the host far
-        # ahead of the GPU: no launch gaps, steady clocks); the one-search-at-a-time loop is kept as "isolated"
-        in_stream = args.resident_streams <= 1 and len(stats) > 0
-        src = stats if in_stream else iso
-        iso_ms_pass1 = sum(s["ms_pass1"] for s in iso) / max(1, len(iso))
-        iso_ms_search = sum(s["ms_search"] for s in iso) / max(1, len(iso))
-        iso_kernel_ms = {k: sum(s[k] for s in iso) / max(1, len(iso)) for k in
-                         ("ms_prep", "ms_pass1", "ms_cert", "ms_pass3", "ms_generic", "ms_resolve")}
-        iso = src
         lf = sum(s["lf_steps"] for s in iso)
         ms_search = sum(s["ms_search"] for s in iso)
         launches = len(iso)
@@ -475,12 +465,7 @@ def main():
                          "algorithmic_bytes_per_launch": bytes1 / max(1, launches),
                          "lf_steps_per_launch": lf1 / max(1, launches), "seed_lookups_per_launch": seeds1 / max(1, launches),
                          "ms_per_launch": ms_pass1 / max(1, launches),
-                         "timing": ("CUDA events on the stream the kernels run on, inside the timed region of the "
-                                    "device-resident arm (one stream: no overlap between kernels)") if in_stream else
-                                   "CUDA events on the workspace stream, one search at a time (no overlap)",
-                         "isolated": {"ms_per_launch": iso_ms_pass1, "ms_search_per_segment": iso_ms_search,
-                                      "what": "the same searches issued one at a time with a host synchronisation "
-                                              "between them (launch gaps and clock ramps included)"},
+                         "timing": "CUDA events on the workspace stream, one search at a time (no overlap)",
                          "whole_search": {"kernels": "pass 1 + k_free_cert + k_free_chain (pass 3)",
                                           "achieved": bytes_all / (ms_search * 1e-3) / 1e9 if ms_search else None,
                                           "ms_per_segment": ms_search / max(1, launches),
@@ -495,7 +480,6 @@ def main():
                          "frac_random_sector": ((bytes1 / 32) / (ms_pass1 * 1e-3) / probe_indep[32]) if ms_pass1 else None},
             "kernel_ms": {k: sum(s[k] for s in iso) / max(1, launches) for k in
                           ("ms_prep", "ms_pass1", "ms_cert", "ms_pass3", "ms_generic", "ms_resolve")},
-            "kernel_ms_isolated": iso_kernel_ms,
             "trajectory_kernel": {"positions": n0, "ms": st_traj.ms_search, "lf_steps": st_traj.lf_steps,
                                   "queries": st_traj.queries, "positions_per_s": n0 / (st_traj.ms_search * 1e-3)},
         })

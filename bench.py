@@ -229,8 +229,8 @@ def main():
     ap.add_argument("--algo", default="auto")
     ap.add_argument("--k-range", default=None, help="other search range than the metric's 20:200, e.g. 12:255 "
                     "(BASELINE configs[4]); the JSON line then says so in config.k_range")
-    ap.add_argument("--resident-streams", type=int, default=int(os.environ.get("NEWMAP_B200_RESIDENT_STREAMS", "1")),
-                    help="CUDA streams the device-resident arm deals its workspaces over")
+    ap.add_argument("--resident-streams", type=int, default=int(os.environ.get("NEWMAP_B200_RESIDENT_STREAMS", "0")),
+                    help="CUDA streams the device-resident arm deals its workspaces over (0 = every workspace its own stream)")
     ap.add_argument("--e2e-depth", type=int, default=int(os.environ.get("NEWMAP_B200_E2E_DEPTH", "4")),
                     help="workspaces (streams) the end-to-end arm pipelines over")
     args = ap.parse_args()
@@ -307,14 +307,14 @@ def main():
     max_len = max(len(s.data) for s, _ in segs)
     stream = torch.cuda.current_stream()
 
-    # ---- device-resident arm: one workspace per segment, dealt over --resident-streams torch streams (1 = all on
-    # torch's current stream, kernels of a step strictly one after the other)
+    # ---- device-resident arm: one workspace per segment.  --resident-streams 0 (default): every workspace on the
+    # stream the library creates for it (kernels of different segments overlap); N >= 1: dealt over N torch streams
+    # (1 = the kernels of a step strictly one after the other)
     resident = []
     pinned_in = []
-    side = [torch.cuda.Stream() for _ in range(args.resident_streams)] if args.resident_streams > 1 else []
+    side = [torch.cuda.Stream() for _ in range(args.resident_streams)]
     for j, (seg, n) in enumerate(segs):
-        ws_stream = side[j % len(side)] if side else stream
-        ws = _lib.Workspace(index, len(seg.data), cuda_stream=ws_stream.cuda_stream)
+        ws = _lib.Workspace(index, len(seg.data), cuda_stream=side[j % len(side)].cuda_stream if side else None)
         pb = _lib.PinnedBuffer(len(seg.data))
         pb.array[:] = np.frombuffer(seg.data, dtype=np.uint8)
         ws.upload(pb.ptr, len(seg.data))
@@ -485,7 +485,7 @@ def main():
         })
         line["config"]["l2"] = "index (rank32 + seed table) larger than L2 except for c2_100m (rank32 50 MB); no flush"
         line["config"]["segments_per_step_per_gpu"] = S
-        line["config"]["resident_streams"] = max(1, args.resident_streams)
+        line["config"]["resident_streams"] = args.resident_streams or "one per workspace (%d)" % len(resident)
         if world == 1:
             # the whole `newmap search` run a user makes: FASTA file in, <id>.unique.uint8 files out (device ingest path)
             line["file_to_file"] = file_to_file_run(fa, ix_path, local)

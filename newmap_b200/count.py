@@ -39,12 +39,14 @@ def close_all() -> None:
 
 
 def _check_threads(num_threads) -> None:
-    # the reference parses num_threads with the 'b' format (newmap-count.c:36,102): 0..255 or OverflowError.
-    # Accepted for interface compatibility and otherwise ignored on the GPU.
-    if not isinstance(num_threads, int) or isinstance(num_threads, bool) and False:
-        raise TypeError("an integer is required")
-    if not 0 <= num_threads <= 255:
-        raise OverflowError("unsigned byte integer is out of range")
+    """The reference parses num_threads with the 'b' format (newmap-count.c:36,102): an integer (bool included) in
+    0..255, else TypeError / OverflowError.  Accepted for interface compatibility and otherwise ignored on the GPU."""
+    if not isinstance(num_threads, int):
+        raise TypeError(f"'{type(num_threads).__name__}' object cannot be interpreted as an integer")
+    if num_threads < 0:
+        raise OverflowError("unsigned byte integer is less than minimum")
+    if num_threads > 255:
+        raise OverflowError("unsigned byte integer is greater than maximum")
 
 
 def count_kmers(index_path: str, kmers: list, num_threads: int = 1) -> list:
@@ -68,9 +70,12 @@ def count_kmers(index_path: str, kmers: list, num_threads: int = 1) -> list:
 
 def count_kmers_from_sequence(index_path: str, sequence, indices: list, lengths: list, num_threads: int = 1) -> list:
     """newmap-count.c:91-206: occurrences of sequence[i:i+l] for each (i, l)."""
-    _check_threads(num_threads)
+    # argument parsing order of "sy#OOb" (newmap-count.c:102): the sequence buffer is looked at before num_threads
     if isinstance(sequence, str):
         raise TypeError("a bytes-like object is required, not 'str'")
+    if isinstance(sequence, bytearray):     # 'y#' takes read-only buffers only
+        raise TypeError("argument 2 must be read-only bytes-like object, not bytearray")
+    _check_threads(num_threads)
     if not isinstance(indices, list):
         raise TypeError("Third argument must be a list of integers")
     if not isinstance(lengths, list):
@@ -82,7 +87,17 @@ def count_kmers_from_sequence(index_path: str, sequence, indices: list, lengths:
             raise TypeError("All elements of the the index and length lists must be integers")
         if i < 0:
             raise IndexError("All elements of the the index list must be non-negative integers")
-        if n < 0:
-            raise ValueError("All lengths in the length listlist must be non-negative integers")
+        # newmap-count.c:176-194: a negative length wraps in size_t and fails the bounds check (the ValueError the
+        # source names is unreachable: its test looks at the index again)
+        if n < 0 or i + n > len(sequence):
+            raise IndexError("The sum of the index and length of each k-mer must be less than or equal to the "
+                             "length of the input byte sequence")
     ix = open_index(index_path)
-    return ix.count(sequence, indices, lengths).tolist()
+    # a zero-length k-mer is not an error here (unlike count_kmers): the reference answers 0 for it
+    live = [q for q, n in enumerate(lengths) if n > 0]
+    out = [0] * len(lengths)
+    if live:
+        got = ix.count(sequence, [indices[q] for q in live], [lengths[q] for q in live]).tolist()
+        for q, c in zip(live, got):
+            out[q] = c
+    return out

@@ -45,6 +45,8 @@ READER_THREADS = int(os.environ.get("NEWMAP_B200_READERS", "0"))   # threads rea
 # "host": newmap_b200/fasta.py cuts the segments and every segment is uploaded.  Default: device unless --verbose
 # (the per-sequence statistics of the verbose log need the segment bytes on the host).
 INGEST = os.environ.get("NEWMAP_B200_INGEST", "auto")
+# [(phase name, seconds since the start of the run)] of the last device-ingest run of this process (bench.py reads it)
+LAST_RUN_TRACE: list = []
 
 
 def nil_search_log(*_: str):
@@ -493,8 +495,7 @@ def _write_unique_counts_device(config: SearchConfig, ix: _lib.Index, data_type,
     marks = []
 
     def mark(name):
-        if trace:
-            marks.append((name, time.perf_counter() - t_start))
+        marks.append((name, time.perf_counter() - t_start))
     fa = _lib.Fasta(ix.device, size_hint=path.stat().st_size if path.suffix != ".gz" else 0)
     mark("fasta_open")
     itemsize = data_type.itemsize
@@ -516,7 +517,7 @@ def _write_unique_counts_device(config: SearchConfig, ix: _lib.Index, data_type,
         mark("text_on_device")
         try:
             fa.finish()
-            mark(f"parsed_{fa.info.ms_parse:.1f}ms_device")
+            mark("parsed")
         except RuntimeError:
             return False            # e.g. more header lines than the device parser handles
         if fa.info.odd_whitespace:
@@ -618,6 +619,7 @@ def _write_unique_counts_device(config: SearchConfig, ix: _lib.Index, data_type,
             s_.close()
         fa.close()
         mark("closed")
+        LAST_RUN_TRACE[:] = marks
         if trace:
             print("[newmap_b200 ingest] " + ", ".join(f"{n} {t:.3f}s" for n, t in marks), file=sys.stderr, flush=True)
 

@@ -29,8 +29,8 @@ class Timer:
 
 
 def _counts(index_path, seq: bytes, rcseq, idx: np.ndarray, lens: np.ndarray, nthreads: int, use_rc: bool,
-            timer: Timer | None) -> np.ndarray:
-    mod = ora.ref_modules()[0]
+            timer: Timer | None, mod=None) -> np.ndarray:
+    mod = mod or ora.ref_modules()[0]
     il, ll = idx.tolist(), lens.tolist()
     t0 = time.perf_counter()
     total = np.array(mod.count_kmers_from_sequence(str(index_path), seq, il, ll, nthreads), dtype=np.uint32)
@@ -48,8 +48,10 @@ def _counts(index_path, seq: bytes, rcseq, idx: np.ndarray, lens: np.ndarray, nt
 
 
 def search_segment(index_path, seg: bytes, num_kmers: int, kmer_lengths, is_range: bool, initial: int = 0,
-                   use_rc: bool = True, nthreads: int = 1, timer: Timer | None = None) -> np.ndarray:
-    """uint32 minimum unique lengths of one segment buffer with the reference's control flow."""
+                   use_rc: bool = True, nthreads: int = 1, timer: Timer | None = None, count_module=None) -> np.ndarray:
+    """uint32 minimum unique lengths of one segment buffer with the reference's control flow.  `count_module`: what
+    stands behind `from newmap._c_newmap_count_kmers import count_kmers_from_sequence` (search.py:12) -- the reference's
+    own extension by default; the tests also pass the product's drop-in (newmap_b200.count) to prove the boundary."""
     buf = np.frombuffer(seg, dtype=np.uint8)
     rcseq = seg.translate(COMPLEMENT)[::-1] if use_rc else None
     amb = ~_ALLOWED[buf[:num_kmers]]
@@ -66,7 +68,7 @@ def search_segment(index_path, seg: bytes, num_kmers: int, kmer_lengths, is_rang
         while not finished.all():
             idx = np.nonzero(~finished)[0]
             q = query[idx]
-            c = _counts(index_path, seg, rcseq, idx, q, nthreads, use_rc, timer)
+            c = _counts(index_path, seg, rcseq, idx, q, nthreads, use_rc, timer, count_module)
             one, many = c == 1, c > 1
             u = unique[idx]
             unique[idx] = np.where(one & ((u == 0) | (q < u)), q, u)
@@ -92,7 +94,7 @@ def search_segment(index_path, seg: bytes, num_kmers: int, kmer_lengths, is_rang
             if idx.size == 0:
                 break
             lens = np.minimum(k, len(seg) - idx)
-            c = _counts(index_path, seg, rcseq, idx, lens, nthreads, use_rc, timer)
+            c = _counts(index_path, seg, rcseq, idx, lens, nthreads, use_rc, timer, count_module)
             u = unique[idx]
             unique[idx] = np.where((c == 1) & (u == 0), k, u)
             finished[idx] = c == 1

@@ -24,7 +24,7 @@
 extern "C" {
 #endif
 
-#define NM_ABI_VERSION 2
+#define NM_ABI_VERSION 3
 
 /* error codes (negative = failure, mirroring enum AwFmReturnCode's sign convention,
  * AvxWindowFmIndex/src/AwFmIndex.h:131-137) */
@@ -87,6 +87,11 @@ typedef struct nm_stats {
   uint64_t lf_steps_pass1;    /* part of lf_steps executed by the first pass (every position, depth-capped) */
   uint64_t seed_lookups;      /* seed-table lookups of the trajectory-free search */
   uint64_t seed_lookups_pass1;
+  uint32_t stride;            /* sparse first pass: positions per unconditional seed-table lookup (1 = every window) */
+  uint32_t out_stats;         /* 1 when the four fields below were computed (NM_OPT_OUT_STATS) */
+  uint64_t unique_positions;  /* positions with a non-zero answer */
+  uint64_t ambiguous_positions; /* start positions not in b'ACGTacgt' (search.py:744-766: skipped) */
+  uint32_t min_unique, max_unique; /* smallest / largest non-zero answer; 0 when there is none */
 } nm_stats;
 
 int nm_abi_version(void);
@@ -154,6 +159,11 @@ int nm_workspace_sync(nm_workspace *ws, nm_stats *stats);
                              later passes at once instead of at the depth cap (it is inside a repeat); default 0 = off */
 #define NM_OPT_CERT_RUNS 8 /* certificate pass: runs of consecutive unsettled positions a thread takes per group and strand
                              (one anchor chain each; the rest goes to the third pass); 0 = default 4 */
+#define NM_OPT_STRIDE 9   /* sparse first pass: at most this many positions per unconditional seed-table lookup (the rest is
+                             settled by upper bounds spread from it, or by chains of their own); 0 = as many as the slack
+                             between the table depth and the shortest length allows (at most 8), 1 = every window */
+#define NM_OPT_OUT_STATS 10 /* 1: one more reduction over the output fills stats.unique_positions, ambiguous_positions,
+                             min_unique, max_unique (what `newmap search --verbose` prints per sequence); default 0 */
 int nm_workspace_option(nm_workspace *ws, int option, uint64_t value);
 /* 64-bit FNV-style checksum of the last search's output computed on the device (for
  * device-resident runs that never copy the output back). */

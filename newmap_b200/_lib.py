@@ -34,7 +34,9 @@ class Stats(C.Structure):
                 ("ms_generic", C.c_float), ("ms_resolve", C.c_float), ("ms_d2h", C.c_float), ("ms_total", C.c_float),
                 ("ms_pass1", C.c_float), ("ms_cert", C.c_float), ("ms_pass3", C.c_float), ("launches", C.c_uint32),
                 ("seed_depth", C.c_uint32), ("short_counts", C.c_uint32), ("lf_steps_pass1", C.c_uint64),
-                ("seed_lookups", C.c_uint64), ("seed_lookups_pass1", C.c_uint64)]
+                ("seed_lookups", C.c_uint64), ("seed_lookups_pass1", C.c_uint64), ("stride", C.c_uint32),
+                ("out_stats", C.c_uint32), ("unique_positions", C.c_uint64), ("ambiguous_positions", C.c_uint64),
+                ("min_unique", C.c_uint32), ("max_unique", C.c_uint32)]
 
     def as_dict(self) -> dict:
         return {name: getattr(self, name) for name, _ in self._fields_}
@@ -110,7 +112,7 @@ def load() -> C.CDLL:
         for name, (res, args) in SIGNATURES.items():
             fn = getattr(L, name)
             fn.restype, fn.argtypes = res, args
-        if L.nm_abi_version() != 2:
+        if L.nm_abi_version() != 3:
             raise ImportError("libnewmap_b200.so ABI version mismatch")
         _lib = L
     return _lib
@@ -288,8 +290,10 @@ class Workspace:
             pass
 
     def option(self, name: str, value: int):
-        """'ref_lf' | 'dcap' | 'gsize' | 'pass1' | 'gsize2' | 'own_chains' | 'stall' | 'cert_runs' (NM_OPT_*): instrumentation / tuning, never changes results."""
-        check(load().nm_workspace_option(self._h, {"ref_lf": 1, "dcap": 2, "gsize": 3, "pass1": 4, "gsize2": 5, "own_chains": 6, "stall": 7, "cert_runs": 8}[name], int(value)),
+        """'ref_lf' | 'dcap' | 'gsize' | 'pass1' | 'gsize2' | 'own_chains' | 'stall' | 'cert_runs' | 'stride' | 'out_stats'
+        (NM_OPT_*): instrumentation / tuning, never changes results."""
+        check(load().nm_workspace_option(self._h, {"ref_lf": 1, "dcap": 2, "gsize": 3, "pass1": 4, "gsize2": 5, "own_chains": 6,
+                                                   "stall": 7, "cert_runs": 8, "stride": 9, "out_stats": 10}[name], int(value)),
               "nm_workspace_option")
 
     def attach(self, fasta: "Fasta", seq_offset: int, seg_len: int):

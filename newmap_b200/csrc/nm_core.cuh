@@ -34,6 +34,13 @@ NM_HD int popc64(uint64_t v) {
   return __builtin_popcountll(v);
 #endif
 }
+NM_HD int ctz64(uint64_t v) {  // v != 0
+#if defined(__CUDA_ARCH__)
+  return __ffsll((long long)v) - 1;
+#else
+  return __builtin_ctzll(v);
+#endif
+}
 NM_HD uint64_t ld64(const uint64_t *p) {
 #if defined(__CUDA_ARCH__)
   return __ldg((const unsigned long long *)p);
@@ -80,6 +87,13 @@ NM_HD void atomic_min64(unsigned long long *p, unsigned long long v) {
   if (v < *p) *p = v;
 #endif
 }
+NM_HD void atomic_max64(unsigned long long *p, unsigned long long v) {
+#if defined(__CUDA_ARCH__)
+  atomicMax(p, v);
+#else
+  if (v > *p) *p = v;
+#endif
+}
 NM_HD void atomic_or64(unsigned long long *p, unsigned long long v) {
 #if defined(__CUDA_ARCH__)
   atomicOr(p, v);
@@ -117,6 +131,7 @@ enum { CTR_LF = 0, CTR_QUERIES = 1, CTR_GENERIC = 2, CTR_ANOMALY = 3, CTR_ZERO_K
        CTR_SEEDS = 7,     // seed-table lookups of the trajectory-free search (one 32-byte sector each)
        CTR_SEEDS_PASS1 = 8,  // the part of CTR_SEEDS looked up by the first pass
        CTR_SHORT = 9,     // multi search: positions whose summed count fell below the number of sequences (not 0)
+       CTR_UNIQUE = 10, CTR_AMBIG = 11, CTR_MINLEN = 12, CTR_MAXLEN = 13,  // NM_OPT_OUT_STATS: reductions over the output
        CTR_N = 16 };
 
 struct alignas(8) SeedEntry32 {  // one 64-bit load
@@ -338,11 +353,12 @@ NM_HD uint32_t count_both(const DevIndex &ix, const uint8_t *seg, uint64_t i, ui
 struct SegParams {
   const uint8_t *seg;    // raw bytes, seg_len
   uint8_t *codes;        // seg_len
-  uint32_t *seedkey;     // seg_len: the sl letters starting at p packed 2 bits each (valid unless codes[p] & kSeedBad)
+  uint32_t *pk;          // seg_len/16 + 2 words: the letters packed 2 bits each, position 16w + j in bits 31-2j..30-2j of
+                         // word w (an earlier position is more significant, like the digits of a seed-table key)
   const SeedEntry32 *seedtab;  // seed table the chains start from: 4^sl entries of the file's table ...
   const SeedEntryPair *seedpair;  // ... or of the derived both-strand table (exactly one of the two is set)
   uint32_t sl;           // its depth; kmin >= sl
-  uint32_t *nb;          // seg_len: position of the first barrier >= p inside p's tile, or kNoBarrier
+  uint64_t *barmask;     // ceil(seg_len / kTile): bit j of word t = position t * kTile + j is a barrier
   uint32_t *tile_first;  // ceil(seg_len / kTile): first barrier of the tile, or kNoBarrier
   uint32_t *G;           // seg_len + 1: length of the shortest unique suffix ending at e (forward strand)
   uint32_t *R;           // seg_len: shortest length from i at which the other strand has no match
@@ -361,8 +377,14 @@ struct SegParams {
   uint32_t own_chains;  // chains of their own a certificate thread may run for positions no bound settles
   uint32_t cert_runs;   // certificate pass: runs of consecutive deep entries a thread takes per group and strand
   uint32_t stall;       // first pass: a chain whose interval kept its size for this many steps in a row is left deep (0 = off)
+  uint32_t stride;      // sparse first pass: one seed window per `stride` positions is looked up unconditionally (1 = every window)
 };
 
+NM_HD uint32_t load_out(const SegParams &P, uint32_t i) {
+  if (P.out_width == 1) return reinterpret_cast<const uint8_t *>(P.out)[i];
+  if (P.out_width == 2) return reinterpret_cast<const uint16_t *>(P.out)[i];
+  return reinterpret_cast<const uint32_t *>(P.out)[i];
+}
 NM_HD void store_out(const SegParams &P, uint32_t i, uint32_t v) {
   if (P.out_width == 1) reinterpret_cast<uint8_t *>(P.out)[i] = (uint8_t)v;
   else if (P.out_width == 2) reinterpret_cast<uint16_t *>(P.out)[i] = (uint16_t)v;
@@ -382,8 +404,9 @@ NM_HD void note_zero(const SegParams &P, uint32_t round, uint32_t pos, uint32_t 
 // closed form of search.py:769-871 (see oracle/fm_oracle.c ora_upper_bounds): distance to the next
 // ambiguous START position (first num_kmers bytes only), else to the end of the buffer, capped at max_k
 NM_HD uint32_t next_barrier(const SegParams &P, uint32_t i) {
-  uint32_t v = P.nb[i];
-  if (v != kNoBarrier) return v;
+  const uint64_t m = P.barmask[i / kTile] >> (i % kTile);
+  if (m) return i + (uint32_t)ctz64(m);
+  uint32_t v;
   const uint32_t ntiles = (P.seg_len + kTile - 1) / kTile;
   for (uint32_t t = i / kTile + 1; t < ntiles && (uint64_t)t * kTile < (uint64_t)i + P.kmax; ++t) {
     v = P.tile_first[t];
@@ -531,31 +554,51 @@ NM_HD uint8_t code_of(const SegParams &P, uint32_t p) {
 NM_HD void prep_thread(const DevIndex &ix, const SegParams &P, uint32_t p) {
   (void)ix;
   const uint8_t c0 = code_of(P, p);
-  uint32_t key = 0;
   const uint32_t sl = P.sl;
   bool ok = (uint64_t)p + sl <= P.seg_len;
   if (ok) {
     for (uint32_t j = 0; j < sl; ++j) {
       const uint8_t c = (j == 0) ? c0 : code_of(P, p + j);
       if (c & (kIrregular | kBarrier)) { ok = false; break; }
-      key = (key << 2) | (c & 3u);
     }
   }
   P.codes[p] = ok ? c0 : (uint8_t)(c0 | kSeedBad);
-  P.seedkey[p] = ok ? key : 0u;
 }
 
-// one thread per tile of kTile positions: nb[p] = first barrier at or after p inside the tile
+// one thread per word of pk: the letters of 16 positions, 2 bits each, the earliest position in the top bits
+// (positions beyond the segment read as letter 0; a window that reaches them carries kSeedBad)
+NM_HD void pack_thread(const SegParams &P, uint32_t w) {
+  uint32_t v = 0;
+  for (uint32_t j = 0; j < 16u; ++j) {
+    const uint64_t p = (uint64_t)w * 16u + j;
+    const uint32_t l = p < P.seg_len ? (uint32_t)(P.codes[p] & 3u) : 0u;
+    v = (v << 2) | l;
+  }
+  P.pk[w] = v;
+}
+
+// one thread per tile of kTile positions: barrier bits of the tile, first barrier of the tile
 NM_HD void nb_tile_thread(const SegParams &P, uint32_t t) {
   const uint32_t begin = t * kTile;
   uint32_t end = begin + kTile;
   if (end > P.seg_len) end = P.seg_len;
-  uint32_t next = kNoBarrier;
-  for (uint32_t p = end; p-- > begin;) {
-    if (P.codes[p] & kBarrier) next = p;
-    P.nb[p] = next;
-  }
-  P.tile_first[t] = next;
+  uint64_t m = 0;
+  for (uint32_t p = begin; p < end; ++p)
+    if (P.codes[p] & kBarrier) m |= 1ull << (p - begin);
+  P.barmask[t] = m;
+  P.tile_first[t] = m ? begin + (uint32_t)ctz64(m) : kNoBarrier;
+}
+
+// seed-table key of the window of P.sl letters starting at q (q + P.sl <= seg_len): two words of pk and a funnel shift
+NM_HD uint32_t window_key(const SegParams &P, uint32_t q) {
+  const uint32_t w = q >> 4, r = 2u * (q & 15u);
+  const uint32_t hi = ld32(P.pk + w), lo = ld32(P.pk + w + 1);
+#if defined(__CUDA_ARCH__)
+  const uint32_t x = __funnelshift_l(lo, hi, r);
+#else
+  const uint32_t x = r ? (hi << r) | (lo >> (32u - r)) : hi;
+#endif
+  return x >> (32u - 2u * P.sl);
 }
 
 // seed key of the other strand's k-mer starting (in search order) at i: letters 3-c[i], 3-c[i+1], ...
@@ -613,11 +656,11 @@ NM_HD bool chain_seeded(const SegParams &P, uint32_t kind, uint32_t p) {
   return !(P.codes[p] & kSeedBad);
 }
 NM_HD uint32_t chain_seed_key(const SegParams &P, uint32_t kind, uint32_t p) {
-  return kind == 0u ? P.seedkey[p - P.sl] : rc_seed_key(P.seedkey[p], P.sl);
+  return kind == 0u ? window_key(P, p - P.sl) : rc_seed_key(window_key(P, p), P.sl);
 }
 // seed-table entry of the chain (kind, p): the window of P.sl letters ending at p (forward strand) or starting at p
 NM_HD SeedEntry32 seed_entry(const SegParams &P, uint32_t kind, uint32_t p) {
-  const uint32_t key = P.seedkey[kind == 0u ? p - P.sl : p];
+  const uint32_t key = window_key(P, kind == 0u ? p - P.sl : p);
   if (P.seedpair) {
 #if defined(__CUDA_ARCH__)
     const uint4 e = __ldg(reinterpret_cast<const uint4 *>(P.seedpair + key));
@@ -748,6 +791,114 @@ NM_HD void free_chain_thread(const DevIndex &ix, const uint32_t *C32, const SegP
                  : chain_value(P, run_rc_chain(ix, C32, P, p, cap, steps, seeds), cap, kInf);
     }
     P.R[p] = rr;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Sparse first pass.  The resolver only ever asks "G[e] <= t" and "R[i] <= t" with t >= kmin (range mode: every
+// queried length is >= kmin; list mode: the same except where the segment end cuts a k-mer short, see below), so
+// an UPPER BOUND b <= kmin is as good as the exact value.  Bounds come for free from a neighbour:
+//   G[e+1] <= G[e] + 1   (a unique string stays unique when it is extended; needs position e not to be a barrier)
+//   R[i-1] <= R[i] + 1   (an absent string stays absent when it is extended; needs start i-1 to be wanted)
+// With a seed table of depth sl < kmin a window that is already unique (forward strand) / absent (other strand)
+// at depth sl therefore settles kmin - sl further ends to its right / starts to its left without touching
+// memory.  The positions are cut into cells of `stride` = min(kmin - sl + 1, cap) consecutive ends / starts; a
+// cell is walked in the direction the bounds spread -- ends upwards, starts downwards: the chain of the first
+// position runs (one table lookup, usually decided there), its value spreads as far as it stays <= kmin, the next
+// unsettled position runs its own chain, and so on.  A cell inside a repeat degenerates to one chain per position,
+// which is what the dense pass does everywhere.
+// Exact values are kept where a bound would not do: list mode compares against the CUT length where the segment
+// end truncates a k-mer (search.py:590,600), which may be below kmin -- the end e = seg_len and the starts
+// i > seg_len - kmin get chains of their own there.
+// Stored bounds are valid upper bounds <= kmin, so the later passes (which only rewrite kDeep entries and use
+// G[e-1] + 1 / R[i+1] + 1 as upper bounds themselves) need no change.
+// ---------------------------------------------------------------------------------------------
+constexpr uint32_t kMaxStride = 8;
+// stride chosen when none is asked for: as wide as the slack between the table depth and the shortest length allows
+NM_HD uint32_t sparse_auto_stride(uint32_t kmin, uint32_t sl, bool pair_table, uint32_t asked) {
+  if (!pair_table || kmin <= sl) return 1u;
+  uint32_t s = kmin - sl + 1u;
+  if (s > kMaxStride) s = kMaxStride;
+  if (asked && asked < s) s = asked;
+  return s;
+}
+NM_HD bool sparse_numeric(const SegParams &P, uint32_t v) { return v >= 1u && v <= P.kmax; }
+NM_HD bool sparse_exact_only_end(const SegParams &P, uint32_t e) { return P.mode == 1 && e == P.seg_len; }
+NM_HD bool sparse_exact_only_start(const SegParams &P, uint32_t i) { return P.mode == 1 && P.seg_len - i < P.kmin; }
+
+// ends are grouped [0, head), [head, head + S), ... with head = sl + S - 1: the window of sl letters that starts at
+// q = c * S + (S - 1) ends at the first end of cell c and starts at the last start of cell c (starts [c*S, c*S + S))
+NM_HD uint32_t sparse_fwd_cell_last(const SegParams &P, uint32_t e) {
+  const uint32_t S = P.stride, head = P.sl + S - 1u;
+  uint32_t last = e < head ? head - 1u : head + (e - head) / S * S + (S - 1u);
+  return last > P.seg_len ? P.seg_len : last;
+}
+NM_HD uint32_t sparse_rc_cell_first(const SegParams &P, uint32_t i) { return i / P.stride * P.stride; }
+
+// next end in [cur, last] that needs a chain (the unwanted ones before it are settled as "none"); false = cell done
+NM_HD bool sparse_next_fwd(const SegParams &P, uint32_t &cur, uint32_t last) {
+  for (; cur <= last; ++cur) {
+    if (fwd_wanted(P, cur)) return true;
+    P.G[cur] = kNone;
+  }
+  return false;
+}
+// next start in [first, end1) from the right that needs a chain: on return true it is end1 - 1
+NM_HD bool sparse_next_rc(const SegParams &P, uint32_t first, uint32_t &end1) {
+  for (; end1 > first; --end1) {
+    if (rc_wanted(P, end1 - 1u)) return true;
+    P.R[end1 - 1u] = kInf;
+  }
+  return false;
+}
+// G[cur] = v has just been settled: spread v + 1, v + 2, ... over the ends that follow; returns the first end not settled
+NM_HD uint32_t sparse_spread_fwd(const SegParams &P, uint32_t cur, uint32_t last, uint32_t v) {
+  uint32_t e = cur + 1u;
+  if (!sparse_numeric(P, v)) return e;
+  for (uint32_t b = v + 1u; e <= last && b <= P.kmin && fwd_wanted(P, e) && !sparse_exact_only_end(P, e); ++e, ++b) P.G[e] = b;
+  return e;
+}
+// R[end1 - 1] = v has just been settled: spread over the starts before it; returns the new end1
+NM_HD uint32_t sparse_spread_rc(const SegParams &P, uint32_t first, uint32_t end1, uint32_t v) {
+  uint32_t n = end1 - 1u;   // starts [first, n) remain
+  if (!sparse_numeric(P, v)) return n;
+  for (uint32_t b = v + 1u; n > first && b <= P.kmin && rc_wanted(P, n - 1u) && !sparse_exact_only_start(P, n - 1u); --n, ++b)
+    P.R[n - 1u] = b;
+  return n;
+}
+
+// One cell side walked serially (the readable definition, run by the host-side logic tests; k_pass1_sparse keeps many
+// of these in flight per block and takes the first lookups of all cells of a block together).
+// kind 0: the ends [first_pos, its cell's last]; kind 1: the starts [its cell's first, first_pos].
+NM_HD void sparse_side_thread(const DevIndex &ix, const uint32_t *C32, const SegParams &P, uint32_t kind, uint32_t first_pos,
+                              uint32_t &steps, uint32_t &seeds) {
+  const uint32_t cap = P.dcap < P.kmax ? P.dcap : P.kmax;
+  if (kind == 0u) {
+    uint32_t cur = first_pos;
+    const uint32_t last = sparse_fwd_cell_last(P, first_pos);
+    while (sparse_next_fwd(P, cur, last)) {
+      const uint32_t v = run_chain_pass1(ix, C32, P, 0u, cur, cap, kNone, steps, seeds);
+      P.G[cur] = v;
+      cur = sparse_spread_fwd(P, cur, last, v);
+    }
+  } else {
+    uint32_t end1 = first_pos + 1u;
+    const uint32_t first = sparse_rc_cell_first(P, first_pos);
+    while (sparse_next_rc(P, first, end1)) {
+      const uint32_t v = run_chain_pass1(ix, C32, P, 1u, end1 - 1u, cap, kInf, steps, seeds);
+      P.R[end1 - 1u] = v;
+      end1 = sparse_spread_rc(P, first, end1, v);
+    }
+  }
+}
+// every cell side of a segment, serially: the whole sparse first pass (host-side logic tests)
+NM_HD void sparse_pass1_serial(const DevIndex &ix, const uint32_t *C32, const SegParams &P, uint32_t &steps, uint32_t &seeds) {
+  const uint32_t S = P.stride, head = P.sl + S - 1u;
+  sparse_side_thread(ix, C32, P, 0u, 0u, steps, seeds);                                   // the head cell: ends [0, head)
+  for (uint64_t e = head; e <= P.seg_len; e += S) sparse_side_thread(ix, C32, P, 0u, (uint32_t)e, steps, seeds);
+  for (uint64_t i = 0; i < P.seg_len; i += S) {                                           // starts [i, i + S)
+    const uint64_t top = i + S - 1u < P.seg_len ? i + S - 1u : P.seg_len - 1u;
+    sparse_side_thread(ix, C32, P, 1u, (uint32_t)top, steps, seeds);
   }
 }
 

@@ -59,109 +59,102 @@ __global__ void __launch_bounds__(kBlock) k_count(DevIndex ix, const uint8_t *se
   flush_counter(&counters[CTR_LF], steps);
 }
 
-// prep, fused and vectorised: one thread = 8 consecutive positions, 8 threads = one kTile (64) tile.
-// Writes what prep_thread + nb_tile_thread (nm_core.cuh, kept as the readable definition and for the
-// host-side logic tests) write: codes, packed seed keys (rolling window), next barrier inside the tile,
-// first barrier of the tile.  8-byte / 32-byte stores, tile scan with shuffles.
-constexpr int kPrepV = 8;
-static_assert(kTile == 64 && kPrepV * 8 == (int)kTile, "prep kernel assumes 8 threads x 8 positions per tile");
+// ---------------------------------------------------------------------------------------------
+// prep: raw bytes -> codes (+ kSeedBad), letters packed 2 bits each, barrier bits and first barrier per tile.
+// Writes what prep_thread + pack_thread + nb_tile_thread (nm_core.cuh: the readable definition, run by the
+// host-side logic tests) write.  One block = kPrepTile positions; its bytes (+ the 15 the last seed windows reach
+// into) are brought into shared memory by ONE bulk asynchronous copy (cp.async.bulk, the 1-D TMA path: no
+// per-thread loads of the raw sequence at all), then one thread = 16 positions: 16 codes -> one 16-byte store,
+// their letters -> one word of pk, their barrier bits -> a quarter of a barmask word (combined with shuffles).
+// ---------------------------------------------------------------------------------------------
+constexpr int kPrepV = 16;                      // positions per thread
+constexpr int kPrepTile = kBlock * kPrepV;      // 4096 positions per block
+constexpr int kPrepHalo = 32;                   // bytes after the tile the last windows may read (sl - 1 <= 15)
+static_assert(kTile == 64 && kPrepV * 4 == (int)kTile, "prep kernel assumes 4 threads x 16 positions per tile");
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
 __global__ void __launch_bounds__(kBlock) k_prep(DevIndex ix, SegParams P) {
-  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-  const uint64_t p0 = (uint64_t)t * kPrepV;
+  (void)ix;
+  // raw bytes of the tile from the 16-byte-aligned address at or below its first byte: head (<= 15) + tile + halo
+  __shared__ alignas(128) uint8_t s_raw[kPrepTile + kPrepHalo + 16 + 16];
+  __shared__ alignas(8) unsigned long long s_bar;
+  __shared__ uint8_t s_code[kPrepTile + kPrepHalo];
+  const uint64_t b0 = (uint64_t)blockIdx.x * kPrepTile;                 // first position of the tile
+  const uint8_t *src = P.seg + b0;
+  const uint32_t head = (uint32_t)(reinterpret_cast<uintptr_t>(src) & 15u);
+  const bool have = b0 < P.seg_len;                                     // (the last block may only have pk padding to write)
+  uint64_t want = have ? (uint64_t)P.seg_len - b0 : 0;                  // bytes of the segment from the tile start on
+  if (want > kPrepTile + kPrepHalo) want = kPrepTile + kPrepHalo;
+  // (the buffers behind P.seg are padded: reading up to the next multiple of 16 past the segment end is in bounds)
+  const uint32_t bytes = (uint32_t)((head + want + 15u) & ~15ull);
+  if (have && threadIdx.x == 0) {
+    const uint32_t bar = smem_u32(&s_bar);
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(s_raw)), "l"(src - head), "r"(bytes), "r"(bar) : "memory");
+  }
+  __syncthreads();   // the barrier is initialised before anyone waits on it
+  if (have) {
+    const uint32_t bar = smem_u32(&s_bar);
+    uint32_t done = 0;
+    while (!done) {
+      asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], 0;\n selp.u32 %0, 1, 0, p;\n}"
+                   : "=r"(done) : "r"(bar) : "memory");
+    }
+  }
+  // codes of the tile + halo, each computed once
+  for (uint32_t j = threadIdx.x; j < kPrepTile + kPrepHalo; j += kBlock) {
+    const uint64_t p = b0 + j;
+    uint8_t c = kIrregular;                                             // beyond the segment: invalidates every window that reaches it
+    if (p < P.seg_len) {
+      const uint8_t ch = s_raw[head + j];
+      const unsigned l = letter_of(ch);
+      const bool allowed = start_allowed(ch);
+      c = (uint8_t)l;
+      if (l == 4u || !allowed) c |= kIrregular;
+      if (!allowed) c |= kNoStart;
+      if ((P.mode == 0) ? (!allowed && p < P.num_kmers) : (ch == 'N')) c |= kBarrier;
+    }
+    s_code[j] = c;
+  }
+  __syncthreads();
+  const uint32_t j0 = threadIdx.x * kPrepV;
+  const uint64_t p0 = b0 + j0;
   const uint32_t sl = P.sl;
-  const bool live = p0 < P.seg_len;
-  uint32_t first_barrier = kNoBarrier;
-  unsigned long long cw = 0;  // the thread's 8 codes, one per byte (no dynamically indexed arrays: no local memory)
-  // the block's codes, each computed once, + the sl - 1 codes after them the last windows reach into
-  __shared__ unsigned long long s_code[kBlock + 2];
-  {
-    const uint64_t b0 = (uint64_t)blockIdx.x * blockDim.x * kPrepV;
-    if (live) {
+  // `bad` = characters still to shift out before the window is free of irregular / barrier / out-of-range characters
+  uint32_t bad = 0;
+  for (uint32_t j = 0; j + 1 < sl; ++j) bad = (s_code[j0 + j] & (kIrregular | kBarrier)) ? sl : (bad ? bad - 1 : 0);
+  uint32_t cw[4] = {0, 0, 0, 0}, pkw = 0, barbits = 0;
 #pragma unroll
-      for (int j = 0; j < kPrepV; ++j) {
-        const uint8_t cj = (p0 + j < P.seg_len) ? code_of(P, (uint32_t)(p0 + j)) : (uint8_t)kIrregular;
-        cw |= (unsigned long long)cj << (8 * j);
-      }
-    } else {
-      cw = ~0ull;  // beyond the segment: irregular, invalidates every window that reaches it
-    }
-    s_code[threadIdx.x] = cw;
-    if (threadIdx.x < 16) {
-      const uint64_t q = b0 + (uint64_t)kBlock * kPrepV + threadIdx.x;
-      reinterpret_cast<uint8_t *>(s_code + kBlock)[threadIdx.x] =
-          (q < P.seg_len) ? code_of(P, (uint32_t)q) : (uint8_t)kIrregular;
-    }
-    __syncthreads();
-    if (!live) cw = 0;
+  for (int i = 0; i < kPrepV; ++i) {
+    bad = (s_code[j0 + sl - 1 + i] & (kIrregular | kBarrier)) ? sl : (bad ? bad - 1 : 0);
+    uint32_t c = s_code[j0 + i];
+    pkw = (pkw << 2) | ((p0 + i < P.seg_len) ? (c & 3u) : 0u);
+    if (c & kBarrier) barbits |= 1u << i;
+    if (bad) c |= kSeedBad;
+    cw[i >> 2] |= c << (8 * (i & 3));
   }
-  if (live) {
-    // rolling seed key; `bad` = characters still to shift out before the window is free of irregular /
-    // barrier / out-of-range characters
-    const unsigned long long w1 = s_code[threadIdx.x + 1], w2 = s_code[threadIdx.x + 2];
-    auto code_at = [&](uint32_t j) -> uint32_t {  // code of position p0 + j, j < 24
-      const unsigned long long w = j < 8u ? cw : (j < 16u ? w1 : w2);
-      return (uint32_t)(w >> (8u * (j & 7u))) & 0xFFu;
-    };
-    uint32_t key = 0, bad = 0;
-    const uint32_t keymask = (sl >= 16) ? 0xFFFFFFFFu : ((1u << (2 * sl)) - 1u);
-    auto push = [&](uint32_t j) {
-      const uint32_t cj = code_at(j);
-      key = ((key << 2) | (cj & 3u)) & keymask;
-      bad = (cj & (kIrregular | kBarrier)) ? sl : (bad ? bad - 1 : 0);
-    };
-    for (uint32_t j = 0; j + 1 < sl; ++j) push(j);
-    uint32_t keys[kPrepV];
-    unsigned long long badbits = 0;
-#pragma unroll
-    for (int i = 0; i < kPrepV; ++i) {
-      push(sl - 1 + i);
-      keys[i] = bad ? 0u : key;
-      if (bad) badbits |= (unsigned long long)kSeedBad << (8 * i);
-    }
-    cw |= badbits;
+  if (p0 < P.seg_len) {
     if (p0 + kPrepV <= P.seg_len) {
-      *reinterpret_cast<uint2 *>(P.codes + p0) = make_uint2((uint32_t)cw, (uint32_t)(cw >> 32));
-      uint4 *kd = reinterpret_cast<uint4 *>(P.seedkey + p0);
-      kd[0] = make_uint4(keys[0], keys[1], keys[2], keys[3]);
-      kd[1] = make_uint4(keys[4], keys[5], keys[6], keys[7]);
+      *reinterpret_cast<uint4 *>(P.codes + p0) = make_uint4(cw[0], cw[1], cw[2], cw[3]);
     } else {
 #pragma unroll
-      for (int j = 0; j < kPrepV; ++j)
-        if (p0 + j < P.seg_len) { P.codes[p0 + j] = (uint8_t)(cw >> (8 * j)); P.seedkey[p0 + j] = keys[j]; }
+      for (int i = 0; i < kPrepV; ++i)
+        if (p0 + i < P.seg_len) P.codes[p0 + i] = (uint8_t)(cw[i >> 2] >> (8 * (i & 3)));
     }
-#pragma unroll
-    for (int j = kPrepV - 1; j >= 0; --j)
-      if (p0 + j < P.seg_len && ((cw >> (8 * j)) & kBarrier)) first_barrier = (uint32_t)(p0 + j);
   }
-  // suffix-min over the 8 lanes of the tile: nearest barrier in the lanes to the right of this one
-  uint32_t right = kNoBarrier, incl = first_barrier;
-#pragma unroll
-  for (int o = 1; o < 8; o <<= 1) {
-    const uint32_t v = __shfl_down_sync(0xffffffffu, incl, o, 8);
-    if ((threadIdx.x & 7) + o < 8) incl = min(incl, v);
+  if (p0 < (uint64_t)P.seg_len + 32u) P.pk[p0 >> 4] = pkw;              // pk has seg_len / 16 + 2 words
+  // barrier bits of the 64-position tile: 4 lanes x 16 bits
+  unsigned long long m = (unsigned long long)barbits << (16 * (threadIdx.x & 3));
+  m |= __shfl_xor_sync(0xffffffffu, m, 1);
+  m |= __shfl_xor_sync(0xffffffffu, m, 2);
+  if ((threadIdx.x & 3) == 0 && p0 < P.seg_len) {
+    P.barmask[p0 / kTile] = m;
+    P.tile_first[p0 / kTile] = m ? (uint32_t)p0 + (uint32_t)(__ffsll((long long)m) - 1) : kNoBarrier;
   }
-  {
-    const uint32_t v = __shfl_down_sync(0xffffffffu, incl, 1, 8);
-    if ((threadIdx.x & 7) + 1 < 8) right = v;
-  }
-  if (!live) return;
-  uint32_t next = right, nbv[kPrepV];
-#pragma unroll
-  for (int j = kPrepV - 1; j >= 0; --j) {
-    if (p0 + j < P.seg_len && ((cw >> (8 * j)) & kBarrier)) next = (uint32_t)(p0 + j);
-    nbv[j] = next;
-  }
-  if (p0 + kPrepV <= P.seg_len) {
-    uint4 *nd = reinterpret_cast<uint4 *>(P.nb + p0);
-    nd[0] = make_uint4(nbv[0], nbv[1], nbv[2], nbv[3]);
-    nd[1] = make_uint4(nbv[4], nbv[5], nbv[6], nbv[7]);
-  } else {
-#pragma unroll
-    for (int j = 0; j < kPrepV; ++j)
-      if (p0 + j < P.seg_len) P.nb[p0 + j] = nbv[j];
-  }
-  if ((threadIdx.x & 7) == 0) P.tile_first[p0 / kTile] = incl;
 }
 
 __global__ void __launch_bounds__(kBlock) k_trajectory(DevIndex ix, SegParams P) {
@@ -200,118 +193,133 @@ __global__ void __launch_bounds__(kBlock, 8) k_free_chain(DevIndex ix, SegParams
   flush_counter(&P.counters[first ? CTR_SEEDS_PASS1 : CTR_SEEDS], seeds);
 }
 
-// pass 1, tiled: one block = kP1Tile consecutive positions = 2 * kP1Tile chains (forward strand ending at p, other
-// strand starting at p).  With a deep seed table most chains are over after their table lookup, so:
-//   phase A  every thread issues its four seed lookups back to back (four independent random sectors in flight per
-//            thread, no divergence), settles the chains that are already decided and queues the rest in shared memory;
-//   phase B  the lanes pop queued chains and extend them one step per iteration, taking the next chain as soon as
-//            theirs ends, so the warps stay full while the DRAM latency of each step is covered by the other lanes.
-// Same values as free_chain_thread(first = true) (nm_core.cuh) position by position.
-constexpr int kP1Win = 2;  // seed windows per thread (3 or 4: shorter kernel when timed alone, slower job: 8.62 -> 7.98 G positions/s)
-constexpr int kP1Tile = kP1Win * kBlock;
+// ---------------------------------------------------------------------------------------------
+// pass 1, sparse (nm_core.cuh "Sparse first pass"; sparse_side_thread is the serial definition of what one cell
+// side does).  One block = kSpCells * kBlock cells of P.stride positions; a cell has a forward side (its ends,
+// walked upwards) and an other-strand side (its starts, walked downwards), and ONE window of the both-strand table
+// -- the one that ends at the cell's first end and starts at its last start -- opens both.
+//   phase A  every thread issues the table lookups of its cells back to back (independent random sectors in
+//            flight, no divergence) and walks each side as far as it goes without touching the index again: with a
+//            deep table most cells are finished here, one 16-byte access for `stride` positions and both strands;
+//   phase B  the sides that are not finished are queued in shared memory; the lanes pop them and run them to their
+//            end, one memory access per loop iteration whatever the side is doing -- a table lookup for the next
+//            unsettled position or one backward-extension step of its chain -- with the addresses computed first
+//            and the 32-byte loads issued in one place, so lanes in different states share an iteration.
+// ---------------------------------------------------------------------------------------------
+constexpr int kSpCells = 2;                              // cells per thread
+constexpr int kSpItems = 2 * kSpCells * kBlock + 8;      // sides a block can queue (+ the head cell of block 0)
 
-__global__ void __launch_bounds__(kBlock, 8) k_pass1_tiled(DevIndex ix, SegParams P) {
+__global__ void __launch_bounds__(kBlock, 6) k_pass1_sparse(DevIndex ix, SegParams P) {
   __shared__ uint32_t sC[8];
-  __shared__ uint4 s_items[2 * kP1Tile + 16];  // {p, lo, hi, d | kind << 31}; + the seedless ends of block 0
+  __shared__ uint4 s_items[kSpItems];    // {position, lo, hi, depth | kind << 31 | needs-seed << 30}
+  __shared__ uint32_t s_limit[kSpItems]; // last end of the cell (forward side) / first start of the cell (other strand)
   __shared__ uint32_t s_count, s_next;
   if (threadIdx.x == 0) s_count = s_next = 0;
   const uint32_t *C32 = stage_c32(ix, sC);  // __syncthreads inside
   const uint32_t cap = P.dcap < P.kmax ? P.dcap : P.kmax;
-  const uint32_t t0 = blockIdx.x * kP1Tile;
+  const uint32_t S = P.stride, sl = P.sl;
+  const uint32_t *pair_words = reinterpret_cast<const uint32_t *>(P.seedpair);
   uint32_t steps = 0, seeds = 0;
 
-  // ---- phase A.  Thread work = two seed windows q (letters q .. q+sl-1); a window seeds the other-strand chain that
-  // STARTS at q and the forward-strand chain that ENDS at q + sl, so with the both-strand table one 16-byte entry
-  // serves two chains.  Code bytes first, then keys, then entries: the loads of each group are in flight together.
-  SeedEntry32 ent[2 * kP1Win];
-  uint32_t st[2 * kP1Win];  // 0 outside the segment, 1 not wanted, 2 starts from a letter, 3 starts from the seed table
+  auto push = [&](uint32_t kind, uint32_t pos, uint32_t limit, const ChainState &s, bool need_seed) {
+    const uint32_t at = atomicAdd(&s_count, 1u);
+    s_items[at] = make_uint4(pos, s.lo, s.hi, s.d | (kind << 31) | (need_seed ? 1u << 30 : 0u));
+    s_limit[at] = limit;
+  };
+  // the value v of `pos` is known: store it, spread the bounds it gives, find the side's next position that needs a
+  // chain.  true = the side goes on at `pos` (updated); false = the side is finished
+  auto settle = [&](uint32_t kind, uint32_t &pos, uint32_t limit, uint32_t v) -> bool {
+    if (kind == 0u) {
+      P.G[pos] = v;
+      uint32_t cur = sparse_spread_fwd(P, pos, limit, v);
+      if (!sparse_next_fwd(P, cur, limit)) return false;
+      pos = cur;
+    } else {
+      P.R[pos] = v;
+      uint32_t end1 = sparse_spread_rc(P, limit, pos + 1u, v);
+      if (!sparse_next_rc(P, limit, end1)) return false;
+      pos = end1 - 1u;
+    }
+    return true;
+  };
+  // entry of the both-strand table out of the 32-byte sector that holds it (two entries per sector)
+  auto entry_of = [&](const Rank32Block &sec, uint32_t key, uint32_t kind) -> SeedEntry32 {
+    if (key & 1u) return kind == 0u ? SeedEntry32{(uint32_t)sec.p0, (uint32_t)(sec.p0 >> 32)}
+                                    : SeedEntry32{(uint32_t)sec.p1, (uint32_t)(sec.p1 >> 32)};
+    return kind == 0u ? SeedEntry32{sec.c[0], sec.c[1]} : SeedEntry32{sec.c[2], sec.c[3]};
+  };
+
+  // ---- phase A
   {
-    uint32_t cself[kP1Win], clast[kP1Win];  // codes[q], codes[q + sl - 1]
+    uint64_t q[kSpCells];
+    bool win_ok[kSpCells];
+    uint32_t key[kSpCells];
+    uint4 ent[kSpCells];
 #pragma unroll
-    for (int j = 0; j < kP1Win; ++j) {
-      const uint32_t q = t0 + j * kBlock + threadIdx.x;
-      const uint64_t e = (uint64_t)q + P.sl;
-      cself[j] = q < P.seg_len ? (uint32_t)ld8(P.codes + q) : (uint32_t)(kNoStart | kSeedBad);
-      clast[j] = e <= P.seg_len ? (uint32_t)ld8(P.codes + e - 1) : (uint32_t)kBarrier;
-    }
-    uint32_t key[kP1Win];
-#pragma unroll
-    for (int j = 0; j < kP1Win; ++j) {
-      const uint32_t q = t0 + j * kBlock + threadIdx.x;
-      const uint64_t e = (uint64_t)q + P.sl;
-      const bool window_ok = !(cself[j] & kSeedBad);
-      uint32_t v0 = 0, v1 = 0;
-      if (e <= P.seg_len)  // fwd_wanted / chain_seeded(kind 0) for end e, on the bytes already loaded
-        v0 = !(clast[j] & kBarrier) ? ((window_ok && !(P.mode == 1 && e == P.seg_len)) ? 3u : 2u) : 1u;
-      if (q < P.seg_len)   // rc_wanted / chain_seeded(kind 1) for start q
-        v1 = (P.use_rc && q < P.num_kmers && !(cself[j] & kNoStart)) ? (window_ok ? 3u : 2u) : 1u;
-      st[2 * j] = v0;
-      st[2 * j + 1] = v1;
-      key[j] = (v0 == 3u || v1 == 3u) ? ld32(P.seedkey + q) : 0u;
+    for (int j = 0; j < kSpCells; ++j) {
+      const uint64_t c = ((uint64_t)blockIdx.x * kSpCells + j) * kBlock + threadIdx.x;
+      q[j] = c * S + (S - 1u);            // window of the cell: ends at its first end, starts at its last start
+      win_ok[j] = q[j] + sl <= P.seg_len && !(ld8(P.codes + q[j]) & kSeedBad);
     }
 #pragma unroll
-    for (int j = 0; j < kP1Win; ++j) {
-      ent[2 * j] = ent[2 * j + 1] = SeedEntry32{0u, 0u};
-      if (st[2 * j] == 3u || st[2 * j + 1] == 3u) {
-        if (P.seedpair) {
-          const uint4 e = __ldg(reinterpret_cast<const uint4 *>(P.seedpair + key[j]));
-          ent[2 * j] = SeedEntry32{e.x, e.y};
-          ent[2 * j + 1] = SeedEntry32{e.z, e.w};
-          ++seeds;
-        } else {
-          if (st[2 * j] == 3u) {
-            const uint2 e = __ldg(reinterpret_cast<const uint2 *>(P.seedtab + key[j]));
-            ent[2 * j] = SeedEntry32{e.x, e.y};
-            ++seeds;
+    for (int j = 0; j < kSpCells; ++j) key[j] = win_ok[j] ? window_key(P, (uint32_t)q[j]) : 0u;
+#pragma unroll
+    for (int j = 0; j < kSpCells; ++j) {
+      ent[j] = make_uint4(0u, 0u, 0u, 0u);
+      if (win_ok[j]) {
+        ent[j] = __ldg(reinterpret_cast<const uint4 *>(P.seedpair + key[j]));
+        ++seeds;
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < kSpCells; ++j) {
+      // forward side: ends [q + sl, q + sl + S - 1]
+      const uint64_t e0 = q[j] + sl;
+      if (e0 <= P.seg_len) {
+        uint32_t cur = (uint32_t)e0;
+        const uint32_t last = e0 + S - 1u > P.seg_len ? P.seg_len : (uint32_t)(e0 + S - 1u);
+        if (sparse_next_fwd(P, cur, last)) {
+          if (cur == (uint32_t)e0 && win_ok[j] && !sparse_exact_only_end(P, cur)) {      // chain_seeded(P, 0, cur)
+            const ChainState s = chain_from_seed(SeedEntry32{ent[j].x, ent[j].y}, sl);
+            ChainResult r{0, 0, false};
+            if (!chain_finished(P, 0u, s, r)) push(0u, cur, last, s, false);
+            else if (settle(0u, cur, last, chain_value(P, r, cap, kNone))) push(0u, cur, last, ChainState{0, 0, 0}, true);
+          } else {
+            push(0u, cur, last, ChainState{0, 0, 0}, true);
           }
-          if (st[2 * j + 1] == 3u) {
-            const uint2 e = __ldg(reinterpret_cast<const uint2 *>(P.seedtab + rc_seed_key(key[j], P.sl)));
-            ent[2 * j + 1] = SeedEntry32{e.x, e.y};
-            ++seeds;
+        }
+      }
+      // other-strand side: starts [q - (S - 1), q]
+      const uint64_t first64 = q[j] - (S - 1u);
+      if (first64 < P.seg_len) {
+        const uint32_t first = (uint32_t)first64;
+        uint32_t end1 = q[j] < P.seg_len ? (uint32_t)q[j] + 1u : P.seg_len;
+        if (sparse_next_rc(P, first, end1)) {
+          uint32_t pos = end1 - 1u;
+          if (pos == (uint32_t)q[j] && win_ok[j]) {                                      // chain_seeded(P, 1, pos)
+            const ChainState s = chain_from_seed(SeedEntry32{ent[j].z, ent[j].w}, sl);
+            ChainResult r{0, 0, false};
+            if (!chain_finished(P, 1u, s, r)) push(1u, pos, first, s, false);
+            else if (settle(1u, pos, first, chain_value(P, r, cap, kInf))) push(1u, pos, first, ChainState{0, 0, 0}, true);
+          } else {
+            push(1u, pos, first, ChainState{0, 0, 0}, true);
           }
         }
       }
     }
-  }
-#pragma unroll
-  for (int slot = 0; slot < 2 * kP1Win; ++slot) {
-    const uint32_t kind = slot & 1;
-    const uint32_t p = t0 + (slot >> 1) * kBlock + threadIdx.x + (kind == 0u ? P.sl : 0u);
-    if (st[slot] == 0) continue;
-    uint32_t *dst = kind == 0u ? P.G + p : P.R + p;
-    const uint32_t none = kind == 0u ? kNone : kInf;
-    if (st[slot] == 1) { *dst = none; continue; }
-    const ChainState s = st[slot] == 3 ? chain_from_seed(ent[slot], P.sl) : chain_from_letter(C32, P, kind, p);
-    ChainResult r{0, 0, false};
-    if (chain_finished(P, kind, s, r)) {
-      *dst = chain_value(P, r, cap, none);
-    } else {
-      const uint32_t at = atomicAdd(&s_count, 1u);
-      s_items[at] = make_uint4(p, s.lo, s.hi, s.d | (kind << 31));
-    }
-  }
-  // forward-strand chains that end before the first whole window (e < sl) have no seed: the first block takes them
-  if (blockIdx.x == 0 && threadIdx.x < P.sl && threadIdx.x <= P.seg_len) {
-    const uint32_t e = threadIdx.x;
-    if (fwd_wanted(P, e)) {
-      const ChainState s = chain_from_letter(C32, P, 0u, e);
-      ChainResult r{0, 0, false};
-      if (chain_finished(P, 0u, s, r)) {
-        P.G[e] = chain_value(P, r, cap, kNone);
-      } else {
-        const uint32_t at = atomicAdd(&s_count, 1u);
-        s_items[at] = make_uint4(e, s.lo, s.hi, s.d);
-      }
-    } else {
-      P.G[e] = kNone;
+    // the head cell: the ends [0, sl + S - 1) no window of the grid ends at
+    if (blockIdx.x == 0 && threadIdx.x == 0) {
+      uint32_t cur = 0;
+      const uint32_t last = sparse_fwd_cell_last(P, 0u);
+      if (sparse_next_fwd(P, cur, last)) push(0u, cur, last, ChainState{0, 0, 0}, true);
     }
   }
   __syncthreads();
 
   // ---- phase B
   const uint32_t count = s_count;
-  bool have = false;
-  uint32_t p = 0, kind = 0;
+  bool have = false, need_seed = false;
+  uint32_t kind = 0, pos = 0, limit = 0;
   ChainState s{0, 0, 0};
   StallState stall{0, 0};
   for (;;) {
@@ -319,19 +327,93 @@ __global__ void __launch_bounds__(kBlock, 8) k_pass1_tiled(DevIndex ix, SegParam
       const uint32_t at = atomicAdd(&s_next, 1u);
       if (at >= count) break;
       const uint4 it = s_items[at];
-      p = it.x;
-      s = ChainState{it.y, it.z, it.w & 0x7FFFFFFFu};
+      pos = it.x;
+      limit = s_limit[at];
+      s = ChainState{it.y, it.z, it.w & 0x3FFFFFFFu};
       kind = it.w >> 31;
+      need_seed = (it.w >> 30) & 1u;
       stall = StallState{s.hi - s.lo, 0u};
       have = true;
     }
+    // -- what this iteration does: 0 nothing to load, 1 one step on rank32, 2 table lookup, 3 one step with the letter x
+    uint32_t action = 0, key = 0;
+    unsigned letter = 0;
+    bool done = false;
     ChainResult r{0, 0, false};
-    if (chain_iterate(ix, C32, P, kind, p, s, cap, steps, r)) {
-      *(kind == 0u ? P.G + p : P.R + p) = chain_value(P, r, cap, kind == 0u ? kNone : kInf);
-      have = false;
-    } else if (chain_stalled(P, stall, s)) {      // run_chain_pass1 (nm_core.cuh)
-      *(kind == 0u ? P.G + p : P.R + p) = kDeep;
-      have = false;
+    if (need_seed) {
+      if (chain_seeded(P, kind, pos)) {
+        key = window_key(P, kind == 0u ? pos - sl : pos);
+        action = 2u;
+      } else {
+        s = chain_from_letter(C32, P, kind, pos);
+        stall = StallState{s.hi - s.lo, 0u};
+        need_seed = false;
+      }
+    }
+    if (!need_seed) {
+      if (chain_finished(P, kind, s, r)) {
+        done = true;
+      } else {
+        r.d_hit = 0;
+        r.d_stop = s.d;
+        const bool edge = kind == 0u ? s.d >= pos : pos + s.d >= P.seg_len;
+        if (edge) {
+          r.wall = true;
+          done = true;
+        } else {
+          const uint8_t c = ld8(P.codes + (kind == 0u ? pos - 1u - s.d : pos + s.d));
+          if (c & kBarrier) {
+            r.wall = true;
+            done = true;
+          } else if (s.d >= cap) {
+            done = true;
+          } else {
+            letter = kind == 0u ? (unsigned)(c & kLetterMask) : rc_letter_of_code(c);
+            action = letter < 4u ? 1u : 3u;
+          }
+        }
+      }
+    }
+    // -- the loads of the iteration, in one place
+    Rank32Block A{{0, 0, 0, 0}, 0, 0}, B{{0, 0, 0, 0}, 0, 0};
+    if (action == 1u || action == 2u) {
+      const uint32_t *base = action == 1u ? ix.rank32 : pair_words;
+      const uint32_t ia = action == 1u ? s.lo >> 6 : key >> 1;
+      const uint32_t ib = action == 1u ? s.hi >> 6 : ia;
+      A = ld_rank32(base, ia);
+      B = A;
+      if (ib != ia) B = ld_rank32(base, ib);
+    }
+    // -- what came back
+    bool stalled = false;
+    if (action == 2u) {
+      ++seeds;
+      s = chain_from_seed(entry_of(A, key, kind), sl);
+      stall = StallState{s.hi - s.lo, 0u};
+      need_seed = false;
+      done = chain_finished(P, kind, s, r);
+    } else if (action == 1u) {
+      uint32_t nlo = occ_in_block(A, letter, s.lo & 63u), nhi = occ_in_block(B, letter, s.hi & 63u);
+      if (A.c[0] == kPoison || B.c[0] == kPoison) {      // a block with an x or $ symbol: the unmodified .awfmi block
+        nlo = (uint32_t)occ_native(ix.native, letter, s.lo);
+        nhi = (uint32_t)occ_native(ix.native, letter, s.hi);
+      }
+      const uint32_t c = C32[letter];
+      s.lo = c + nlo;
+      s.hi = c + nhi;
+      ++s.d;
+      ++steps;
+      stalled = chain_stalled(P, stall, s);
+    } else if (action == 3u) {
+      lf_fast(ix, C32, letter, s.lo, s.hi);
+      ++s.d;
+      ++steps;
+      stalled = chain_stalled(P, stall, s);
+    }
+    if (done || stalled) {
+      const uint32_t v = stalled ? kDeep : chain_value(P, r, cap, kind == 0u ? kNone : kInf);
+      if (settle(kind, pos, limit, v)) need_seed = true;
+      else have = false;
     }
   }
   flush_counter(&P.counters[CTR_LF_PASS1], steps);
@@ -384,6 +466,26 @@ __global__ void __launch_bounds__(kBlock) k_resolve(DevIndex ix, SegParams P) {
   uint64_t ref_lf = 0;
   if (i < P.num_kmers) resolve_thread(ix, P, i, ref_lf);
   if (P.want_ref_lf) flush_counter64(&P.counters[CTR_REF_LF], ref_lf);
+}
+
+// NM_OPT_OUT_STATS: what `newmap search --verbose` reports per sequence (search.py:318-347,885-902), reduced on the device
+__global__ void __launch_bounds__(kBlock) k_out_stats(SegParams P) {
+  uint32_t uniq = 0, amb = 0, mn = 0xFFFFFFFFu, mx = 0;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < P.num_kmers; i += (uint64_t)gridDim.x * blockDim.x) {
+    const uint32_t v = load_out(P, (uint32_t)i);
+    if (v) { ++uniq; mn = min(mn, v); mx = max(mx, v); }
+    if (!start_allowed(ld8(P.seg + i))) ++amb;
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    mn = min(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+    mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  }
+  flush_counter(&P.counters[CTR_UNIQUE], uniq);
+  flush_counter(&P.counters[CTR_AMBIG], amb);
+  if ((threadIdx.x & 31) == 0) {
+    if (mx) atomicMax(&P.counters[CTR_MAXLEN], (unsigned long long)mx);
+    if (mn != 0xFFFFFFFFu) atomicMin(&P.counters[CTR_MINLEN], (unsigned long long)mn);
+  }
 }
 
 __global__ void __launch_bounds__(kBlock) k_checksum(const void *out, int width, uint64_t n, unsigned long long *sum) {
@@ -458,7 +560,7 @@ void launch_count(const DevIndex &ix, const uint8_t *seq, const uint64_t *idx, c
 }
 void launch_prep(const DevIndex &ix, const SegParams &P, cudaStream_t st) {
   if (P.seg_len == 0) return;
-  k_prep<<<grid_for(((uint64_t)P.seg_len + kPrepV - 1) / kPrepV), kBlock, 0, st>>>(ix, P);
+  k_prep<<<grid_for((uint64_t)P.seg_len + 32u, kPrepTile), kBlock, 0, st>>>(ix, P);
 }
 void launch_trajectory(const DevIndex &ix, const SegParams &P, cudaStream_t st) {
   if (P.num_kmers == 0) return;
@@ -472,8 +574,10 @@ void launch_free_chain(const DevIndex &ix, const SegParams &P, bool first, cudaS
   k_free_chain<<<grid_for((uint64_t)P.seg_len + 1), kBlock, 0, st>>>(ix, P, first);
 }
 void launch_free_pass1(const DevIndex &ix, const SegParams &P, cudaStream_t st) {
-  const unsigned g = grid_for((uint64_t)P.seg_len, kP1Tile);
-  k_pass1_tiled<<<g ? g : 1u, kBlock, 0, st>>>(ix, P);
+  // cells: the forward sides cover the ends up to seg_len, the other-strand sides the starts below seg_len
+  const uint64_t cells = ((uint64_t)P.seg_len + P.stride) / P.stride + 1u;
+  const unsigned g = grid_for(cells, kSpCells * kBlock);
+  k_pass1_sparse<<<g ? g : 1u, kBlock, 0, st>>>(ix, P);
 }
 void launch_free_cert(const DevIndex &ix, const SegParams &P, cudaStream_t st) {
   const uint32_t ngroups = (uint32_t)(((uint64_t)P.seg_len + 1 + P.gsize - 1) / P.gsize);
@@ -492,6 +596,12 @@ void launch_free_generic(const DevIndex &ix, const SegParams &P, bool all, cudaS
 void launch_resolve(const DevIndex &ix, const SegParams &P, cudaStream_t st) {
   if (P.num_kmers == 0) return;
   k_resolve<<<grid_for(P.num_kmers), kBlock, 0, st>>>(ix, P);
+}
+void launch_out_stats(const SegParams &P, cudaStream_t st) {
+  if (P.num_kmers == 0) return;
+  unsigned g = grid_for(P.num_kmers);
+  if (g > 148 * 8) g = 148 * 8;
+  k_out_stats<<<g, kBlock, 0, st>>>(P);
 }
 void launch_checksum(const void *out, int out_width, uint64_t n, unsigned long long *sum, cudaStream_t st) {
   if (n == 0) return;

@@ -17,12 +17,13 @@ void launch_prep(const DevIndex &ix, const SegParams &P, cudaStream_t st);
 void launch_trajectory(const DevIndex &ix, const SegParams &P, cudaStream_t st);
 void launch_trajectory_multi(const MultiSet *M, const SegParams &P, cudaStream_t st);
 void launch_free_chain(const DevIndex &ix, const SegParams &P, bool first, cudaStream_t st);  // pass 1 / pass 3
-void launch_free_pass1(const DevIndex &ix, const SegParams &P, cudaStream_t st);                 // pass 1, tiled kernel
+void launch_free_pass1(const DevIndex &ix, const SegParams &P, cudaStream_t st);                 // pass 1, sparse kernel
 void launch_free_cert(const DevIndex &ix, const SegParams &P, cudaStream_t st);               // pass 2
 void launch_coarse_anchor(const DevIndex &ix, const SegParams &P, CoarseGroup *groups, cudaStream_t st);
 void launch_coarse_settle(const SegParams &P, const CoarseGroup *groups, cudaStream_t st);
 void launch_free_generic(const DevIndex &ix, const SegParams &P, bool all, cudaStream_t st);
 void launch_resolve(const DevIndex &ix, const SegParams &P, cudaStream_t st);
+void launch_out_stats(const SegParams &P, cudaStream_t st);
 void launch_checksum(const void *out, int out_width, uint64_t n, unsigned long long *sum, cudaStream_t st);
 void launch_probe(const uint8_t *buf, uint64_t n_granules_pow2, uint32_t granule, uint64_t chains, uint32_t steps,
                   uint32_t mlp, bool dependent, unsigned long long *sink, cudaStream_t st);

@@ -56,7 +56,8 @@ struct nm_workspace {
   // device buffers
   uint8_t *d_seg = nullptr, *d_codes = nullptr;
   const uint8_t *seg_ext = nullptr;  // segment attached from a parsed FASTA (nm_workspace_attach) instead of uploaded
-  uint32_t *d_seedkey = nullptr, *d_nb = nullptr, *d_tile_first = nullptr, *d_G = nullptr, *d_R = nullptr;
+  uint32_t *d_pk = nullptr, *d_tile_first = nullptr, *d_G = nullptr, *d_R = nullptr;
+  uint64_t *d_barmask = nullptr;
   void *d_out = nullptr;
   uint32_t *d_klist = nullptr;
   uint32_t klist_cap = 0;
@@ -71,7 +72,7 @@ struct nm_workspace {
   int algo_req = 0, algo_used = 0;
   bool timed_h2d = false, timed_d2h = false;
   void *pending_out = nullptr;
-  uint32_t opt_ref_lf = 0, opt_dcap = 0, opt_gsize = 0, opt_pass1 = 0, opt_gsize2 = ~0u, opt_own_chains = ~0u, opt_stall = ~0u, opt_cert_runs = 0;
+  uint32_t opt_ref_lf = 0, opt_dcap = 0, opt_gsize = 0, opt_pass1 = 0, opt_gsize2 = ~0u, opt_own_chains = ~0u, opt_stall = ~0u, opt_cert_runs = 0, opt_stride = 0, opt_out_stats = 0;
   // several sequences x several indexes (nm_workspace_multi); cleared by the next upload / attach
   nm::CoarseGroup *d_cgroups = nullptr;  // coarse certificate round: 2 per group of >= kMinGsize2 positions
   uint64_t cgroup_cap = 0;
@@ -278,8 +279,8 @@ int ws_alloc(nm_workspace *ws) {
   const uint64_t ntiles = (n + nm::kTile - 1) / nm::kTile + 1;
   NM_CUDA(cudaMalloc((void **)&ws->d_seg, n + 16));
   NM_CUDA(cudaMalloc((void **)&ws->d_codes, n + 16));
-  NM_CUDA(cudaMalloc((void **)&ws->d_seedkey, (n + 1) * 4));
-  NM_CUDA(cudaMalloc((void **)&ws->d_nb, (n + 1) * 4));
+  NM_CUDA(cudaMalloc((void **)&ws->d_pk, (n / 16 + 4) * 4));
+  NM_CUDA(cudaMalloc((void **)&ws->d_barmask, ntiles * 8));
   NM_CUDA(cudaMalloc((void **)&ws->d_tile_first, ntiles * 4));
   NM_CUDA(cudaMalloc((void **)&ws->d_G, (n + 2) * 4));
   NM_CUDA(cudaMalloc((void **)&ws->d_R, (n + 1) * 4));
@@ -302,7 +303,7 @@ int run_search(nm_workspace *ws, int algo) {
   nm_index *ix = ws->ix;
   nm::SegParams &P = ws->P;
   cudaStream_t st = ws->stream;
-  static const unsigned long long init_counters[nm::CTR_N] = {0, 0, 0, 0, ~0ull, 0, 0, 0};
+  static const unsigned long long init_counters[nm::CTR_N] = {0, 0, 0, 0, ~0ull, 0, 0, 0, 0, 0, 0, 0, ~0ull, 0, 0, 0};
   NM_CUDA(cudaMemcpyAsync(ws->d_counters, init_counters, sizeof init_counters, cudaMemcpyHostToDevice, st));
   NM_CUDA(cudaEventRecord(ws->ev[EV_H2D1], st));
   nm::launch_prep(ix->dev, P, st);
@@ -340,9 +341,11 @@ int run_search(nm_workspace *ws, int algo) {
     if (fast) {
       // tiled kernel when the chains are short (deep seed table); with the file's 12-letter table the chains run
       // 4-5 steps on average and one thread per position is faster (measured: profiles/r1_seed_depth_sweep.md)
-      const bool tiled = ws->opt_pass1 == 2u || (ws->opt_pass1 == 0u && P.sl >= 13u);
-      if (tiled) nm::launch_free_pass1(ix->dev, P, st);
-      else nm::launch_free_chain(ix->dev, P, true, st);
+      // the sparse kernel needs the both-strand table; one thread per position otherwise (the file's 12-letter table:
+      // chains of 4-5 steps) or when asked for (NM_OPT_PASS1 = 1: the dense reference of the tests)
+      const bool sparse = P.seedpair != nullptr && ws->opt_pass1 != 1u;
+      if (sparse) nm::launch_free_pass1(ix->dev, P, st);
+      else { P.stride = 1; nm::launch_free_chain(ix->dev, P, true, st); }
       ++ws->launches;
     }
     NM_CUDA(cudaEventRecord(ws->ev[EV_PASS1], st));
@@ -363,6 +366,10 @@ int run_search(nm_workspace *ws, int algo) {
     nm::launch_resolve(ix->dev, P, st);
     ws->launches += P.num_kmers ? 1u : 0u;
     NM_CUDA(cudaEventRecord(ws->ev[EV_RESOLVE1], st));
+  }
+  if (ws->opt_out_stats) {
+    nm::launch_out_stats(P, st);
+    ws->launches += P.num_kmers ? 1u : 0u;
   }
   NM_CUDA(cudaGetLastError());
   NM_CUDA(cudaMemcpyAsync(ws->h_counters, ws->d_counters, nm::CTR_N * 8, cudaMemcpyDeviceToHost, st));
@@ -522,8 +529,8 @@ void nm_workspace_destroy(nm_workspace *ws) {
   cudaStreamSynchronize(ws->stream);
   cudaFree(ws->d_seg);
   cudaFree(ws->d_codes);
-  cudaFree(ws->d_seedkey);
-  cudaFree(ws->d_nb);
+  cudaFree(ws->d_pk);
+  cudaFree(ws->d_barmask);
   cudaFree(ws->d_tile_first);
   cudaFree(ws->d_G);
   cudaFree(ws->d_R);
@@ -648,8 +655,8 @@ int nm_workspace_search(nm_workspace *ws, uint64_t num_kmers, int mode, const ui
   nm::SegParams &P = ws->P;
   P.seg = ws->seg_ext ? ws->seg_ext : ws->d_seg;
   P.codes = ws->d_codes;
-  P.seedkey = ws->d_seedkey;
-  P.nb = ws->d_nb;
+  P.pk = ws->d_pk;
+  P.barmask = ws->d_barmask;
   P.tile_first = ws->d_tile_first;
   P.G = ws->d_G;
   P.R = ws->d_R;
@@ -685,6 +692,8 @@ int nm_workspace_search(nm_workspace *ws, uint64_t num_kmers, int mode, const ui
     // pass's LF steps on the 1 Gbp bench genome, but those are the cheap ones (neighbouring positions inside a repeat
     // walk the same rank blocks, L2 hits) and the later passes pay more than it saves (8.45 -> 8.03 G positions/s).
     P.stall = P.dcap < kmax ? (ws->opt_stall == ~0u ? 0u : ws->opt_stall) : 0u;
+    // sparse first pass (nm_core.cuh): one window per `stride` positions, the rest settled by bounds spread from it
+    P.stride = nm::sparse_auto_stride(kmin, sl, deep, ws->opt_stride);
   }
   if (ws->multi_ix) algo = NM_ALGO_TRAJECTORY;  // the summed count is searched on the reference's own trajectory
   ws->algo_req = algo;
@@ -753,6 +762,14 @@ int nm_workspace_sync(nm_workspace *ws, nm_stats *stats) {
     stats->seed_lookups_pass1 = seeds_pass1;
     stats->launches = ws->launches + (replayed ? free_launches : 0u);
     stats->seed_depth = ws->P.sl;
+    stats->stride = ws->P.stride;
+    if (ws->opt_out_stats) {
+      stats->out_stats = 1;
+      stats->unique_positions = ws->h_counters[nm::CTR_UNIQUE];
+      stats->ambiguous_positions = ws->h_counters[nm::CTR_AMBIG];
+      stats->min_unique = ws->h_counters[nm::CTR_MINLEN] == ~0ull ? 0u : (uint32_t)ws->h_counters[nm::CTR_MINLEN];
+      stats->max_unique = (uint32_t)ws->h_counters[nm::CTR_MAXLEN];
+    }
     stats->short_counts = (uint32_t)std::min<unsigned long long>(ws->h_counters[nm::CTR_SHORT], 0xFFFFFFFFull);
     stats->ms_pass1 = ms[7];
     stats->ms_cert = ms[8];
@@ -795,6 +812,8 @@ int nm_workspace_option(nm_workspace *ws, int option, uint64_t value) {
     case NM_OPT_STALL: if (value > 64) return NM_EARG; ws->opt_stall = (uint32_t)value; return NM_OK;
     case NM_OPT_CERT_RUNS: if (value > 64) return NM_EARG; ws->opt_cert_runs = (uint32_t)value; return NM_OK;
     case NM_OPT_GSIZE2: if (value > 65536) return NM_EARG; ws->opt_gsize2 = (uint32_t)value; return NM_OK;
+    case NM_OPT_OUT_STATS: ws->opt_out_stats = value ? 1u : 0u; return NM_OK;
+    case NM_OPT_STRIDE: if (value > nm::kMaxStride) return NM_EARG; ws->opt_stride = (uint32_t)value; return NM_OK;
     default: return NM_EARG;
   }
 }

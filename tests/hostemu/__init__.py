@@ -31,7 +31,7 @@ def lib():
         L.emu_count.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p, C.c_uint64, C.c_int,
                                 C.c_void_p, C.c_void_p]
         L.emu_min_unique.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_int, C.c_void_p, C.c_uint32,
-                                     C.c_uint32, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32]
+                                     C.c_uint32, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32]
         L.emu_min_unique_multi.argtypes = [C.POINTER(C.c_void_p), C.c_uint32, C.POINTER(C.c_void_p), C.c_uint32, C.c_uint32,
                                            C.c_uint32, C.c_int, C.c_void_p, C.c_uint32, C.c_uint32, C.c_int, C.c_int,
                                            C.c_void_p, C.c_void_p]
@@ -79,11 +79,12 @@ class EmuIndex:
         return out, lf.value
 
     def min_unique_segment(self, seg: bytes, num_kmers, kmer_lengths, is_range, initial=0, use_rc=True, algo=0,
-                           out_width=4, dcap=0, gsize=0, gsize2=0, stall=0):
+                           out_width=4, dcap=0, gsize=0, gsize2=0, stall=0, stride=0):
+        """stride: 0 = widest the slack allows (default of the library), n = at most n, -1 = dense thread-per-position pass."""
         buf = np.frombuffer(seg, dtype=np.uint8)
         kl = np.array([min(kmer_lengths), max(kmer_lengths)] if is_range else list(kmer_lengths), dtype=np.uint32)
         out = np.zeros(max(num_kmers, 1), dtype={1: np.uint8, 2: np.uint16, 4: np.uint32}[out_width])
-        stats = np.zeros(8, dtype=np.int64)
+        stats = np.zeros(10, dtype=np.int64)
         lib().emu_min_unique(self._h, buf.ctypes.data, buf.size, num_kmers, 0 if is_range else 1, kl.ctypes.data,
-                             kl.size, initial, int(use_rc), algo, out_width, out.ctypes.data, stats.ctypes.data, dcap, gsize, gsize2, stall)
+                             kl.size, initial, int(use_rc), algo, out_width, out.ctypes.data, stats.ctypes.data, dcap, gsize, gsize2, stall, stride & 0xFFFFFFFF)
         return out[:num_kmers], stats

@@ -100,15 +100,17 @@ int emu_count(EmuIndex *ix, const uint8_t *seq, uint64_t seq_len, const uint64_t
   return 0;
 }
 
-// stats: [0] lf, [1] queries, [2] generic searches, [3] anomaly, [4] zero pos (-1), [5] zero len, [6] zero round, [7] ref lf
+// stats: [0] lf, [1] queries, [2] generic searches, [3] anomaly, [4] zero pos (-1), [5] zero len, [6] zero round, [7] ref lf,
+//        [8] seed-table lookups, [9] stride of the sparse first pass
 int emu_min_unique(EmuIndex *ix, const uint8_t *seg, uint32_t seg_len, uint32_t num_kmers, int mode,
                    const uint32_t *klist, uint32_t nk, uint32_t initial, int use_rc, int algo, int out_width,
-                   void *out, int64_t *stats, uint32_t dcap, uint32_t gsize, uint32_t gsize2, uint32_t stall) {
+                   void *out, int64_t *stats, uint32_t dcap, uint32_t gsize, uint32_t gsize2, uint32_t stall, uint32_t stride) {
   std::vector<uint8_t> codes(seg_len + 16);
-  std::vector<uint32_t> seedkey(seg_len + 1), nb(seg_len + 1), tf((seg_len + kTile - 1) / kTile + 1), G(seg_len + 2), R(seg_len + 1);
+  std::vector<uint32_t> pk(seg_len / 16 + 2), tf((seg_len + kTile - 1) / kTile + 1), G(seg_len + 2), R(seg_len + 1);
+  std::vector<uint64_t> barmask((seg_len + kTile - 1) / kTile + 1);
   unsigned long long ctr[CTR_N] = {0, 0, 0, 0, ~0ull, 0, 0, 0};
   SegParams P{};
-  P.seg = seg; P.codes = codes.data(); P.seedkey = seedkey.data(); P.nb = nb.data(); P.tile_first = tf.data();
+  P.seg = seg; P.codes = codes.data(); P.pk = pk.data(); P.barmask = barmask.data(); P.tile_first = tf.data();
   P.G = G.data(); P.R = R.data(); P.out = out; P.klist = klist; P.counters = ctr;
   P.seg_len = seg_len; P.num_kmers = num_kmers; P.nk = nk; P.initial = initial; P.mode = mode;
   P.use_rc = use_rc; P.out_width = out_width;
@@ -126,7 +128,10 @@ int emu_min_unique(EmuIndex *ix, const uint8_t *seg, uint32_t seg_len, uint32_t 
   P.want_ref_lf = deep ? 0 : 1;
   P.dcap = dcap ? dcap : P.sl + 12; if (P.dcap <= P.sl) P.dcap = P.sl + 1;
   P.stall = P.dcap < P.kmax ? stall : 0;
+  // nm_lib.cu: 0 = the widest stride the slack allows; 0xFFFFFFFF = the dense thread-per-position first pass
+  P.stride = stride == 0xFFFFFFFFu ? 1u : sparse_auto_stride(P.kmin, P.sl, deep, stride);
   for (uint32_t p = 0; p < seg_len; ++p) prep_thread(ix->dev, P, p);
+  for (uint32_t w = 0; w < seg_len / 16 + 2; ++w) pack_thread(P, w);
   const uint32_t ntiles = (seg_len + kTile - 1) / kTile;
   for (uint32_t t = 0; t < ntiles; ++t) nb_tile_thread(P, t);
   uint32_t steps = 0, nq = 0, ns = 0, seeds = 0;
@@ -137,7 +142,8 @@ int emu_min_unique(EmuIndex *ix, const uint8_t *seg, uint32_t seg_len, uint32_t 
     const bool fast = (algo != 2) && ix->has_rank32 && P.kmin >= ix->dev.seed_len;
     P.fast = fast;
     if (fast) {
-      for (uint32_t p = 0; p <= seg_len; ++p) free_chain_thread(ix->dev, ix->c32, P, p, true, steps, seeds);
+      if (deep && stride != 0xFFFFFFFFu) sparse_pass1_serial(ix->dev, ix->c32, P, steps, seeds);   // k_pass1_sparse
+      else for (uint32_t p = 0; p <= seg_len; ++p) free_chain_thread(ix->dev, ix->c32, P, p, true, steps, seeds);
       if (P.dcap < P.kmax) {
         uint32_t s2 = 0;
         if (gsize2 > P.gsize) {  // nm_lib.cu run_search: coarse round (anchor chains at fixed positions, containment only)
@@ -163,7 +169,7 @@ int emu_min_unique(EmuIndex *ix, const uint8_t *seg, uint32_t seg_len, uint32_t 
   }
   if (stats) {
     stats[0] = steps; stats[1] = nq; stats[2] = ns; stats[3] = (int64_t)ctr[CTR_ANOMALY];
-    stats[4] = -1; stats[5] = 0; stats[6] = -1; stats[7] = (int64_t)ref_lf;
+    stats[4] = -1; stats[5] = 0; stats[6] = -1; stats[7] = (int64_t)ref_lf; stats[8] = seeds; stats[9] = P.stride;
     if (ctr[CTR_ZERO_KEY] != ~0ull) {
       stats[4] = (int64_t)(ctr[CTR_ZERO_KEY] & 0xFFFFFFFFull);
       stats[6] = (int64_t)(ctr[CTR_ZERO_KEY] >> 32);
@@ -180,18 +186,20 @@ int emu_min_unique_multi(EmuIndex *const *ixs, uint32_t n_ix, const uint8_t *con
                          int out_width, void *out, int64_t *stats) {
   if (n_ix == 0 || n_ix > kMaxMulti || n_seq == 0 || n_seq > kMaxMulti) return -1;
   std::vector<uint8_t> codes(seg_len + 16);
-  std::vector<uint32_t> seedkey(seg_len + 1), nb(seg_len + 1), tf((seg_len + kTile - 1) / kTile + 1), G(seg_len + 2), R(seg_len + 1);
+  std::vector<uint32_t> pk(seg_len / 16 + 2), tf((seg_len + kTile - 1) / kTile + 1), G(seg_len + 2), R(seg_len + 1);
+  std::vector<uint64_t> barmask((seg_len + kTile - 1) / kTile + 1);
   unsigned long long ctr[CTR_N] = {0, 0, 0, 0, ~0ull, 0, 0, 0};
   SegParams P{};
-  P.seg = segs[0]; P.codes = codes.data(); P.seedkey = seedkey.data(); P.nb = nb.data(); P.tile_first = tf.data();
+  P.seg = segs[0]; P.codes = codes.data(); P.pk = pk.data(); P.barmask = barmask.data(); P.tile_first = tf.data();
   P.G = G.data(); P.R = R.data(); P.out = out; P.klist = klist; P.counters = ctr;
   P.seg_len = seg_len; P.num_kmers = num_kmers; P.nk = nk; P.initial = initial; P.mode = mode;
   P.use_rc = use_rc; P.out_width = out_width; P.gsize = 16;
   if (mode == 0) { P.kmin = klist[0]; P.kmax = klist[1]; }
   else { P.kmin = P.kmax = klist[0]; for (uint32_t j = 0; j < nk; ++j) { if (klist[j] < P.kmin) P.kmin = klist[j]; if (klist[j] > P.kmax) P.kmax = klist[j]; } }
   const DevIndex &d0 = ixs[0]->dev;
-  P.sl = d0.seed_len; P.seedtab = d0.seed32; P.seedpair = nullptr; P.dcap = P.sl + 12;
+  P.sl = d0.seed_len; P.seedtab = d0.seed32; P.seedpair = nullptr; P.dcap = P.sl + 12; P.stride = 1;
   for (uint32_t p = 0; p < seg_len; ++p) prep_thread(d0, P, p);
+  for (uint32_t w = 0; w < seg_len / 16 + 2; ++w) pack_thread(P, w);
   const uint32_t ntiles = (seg_len + kTile - 1) / kTile;
   for (uint32_t t = 0; t < ntiles; ++t) nb_tile_thread(P, t);
   MultiSet M{};

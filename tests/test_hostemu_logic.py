@@ -248,3 +248,44 @@ def test_diverged_repeats_interpolation_certificate(tmp_path):
                                                    gsize2=(0, 48, 256)[(dcap_extra + gsize) % 3], stall=(1, 2, 0, 3)[gsize % 4])
                     bad = np.nonzero(got != want)[0]
                     assert bad.size == 0, (trial, batch, dcap_extra, gsize, bad[:10], got[bad[:10]], want[bad[:10]])
+
+
+@pytest.mark.parametrize("stride", [0, 2, 3, 5, 8, -1])
+def test_sparse_first_pass_is_exact_for_any_stride(manifest, golden_searches, stride):
+    """The sparse first pass (one seed window per `stride` positions looked up unconditionally, upper bounds
+    G[e+1] <= G[e]+1 / R[i-1] <= R[i]+1 spread from it, chains of their own only for what no bound settles) gives the
+    reference's bytes for every stride, in range and in list mode (incl. the end-of-buffer truncation of list mode,
+    where a bound would not do), and looks up fewer windows than the dense pass."""
+    cache, sparse_runs, lookups = {}, 0, [0, 0]
+    for run in manifest["searches"]:
+        seed = manifest["indexes"][run["index"]]["seed_length"]
+        klist = run_klist(run)
+        depth = min(seed + 1 + run["id"] % 3, 16)
+        key = (run["index"], depth)
+        ix = cache.get(key)
+        if ix is None:
+            ix = cache[key] = EmuIndex(GOLD / f"{run['index']}.awfmi").set_seed_depth(depth)
+        got = {}
+        for seg, n in _segments(run):
+            out, stats = ix.min_unique_segment(seg.data, n, klist, run["range"], run.get("initial", 0),
+                                               not run.get("norc", False), 0, stride=stride,
+                                               dcap=depth + 1 + run["id"] % 7, gsize=(20, 5, 64)[run["id"] % 3])
+            assert stats[3] == 0 and stats[4] == -1, (run["id"], stats)
+            if min(klist) > depth and stride >= 0:
+                want_stride = min(min(klist) - depth + 1, 8, stride or 8)
+                assert stats[9] == want_stride, (run["id"], stats[9], want_stride)
+                sparse_runs += want_stride > 1
+                if stride == 0 and want_stride > 1:
+                    lookups[0] += stats[8]
+                    lookups[1] += ix.min_unique_segment(seg.data, n, klist, run["range"], run.get("initial", 0),
+                                                        not run.get("norc", False), 0, stride=-1)[1][8]
+            got.setdefault(seg.id, []).append(out)
+        for sid, parts in got.items():
+            want = golden_searches[f"run{run['id']}|{sid.decode()}"]
+            arr = np.concatenate(parts)
+            bad = np.nonzero(arr != want)[0]
+            assert bad.size == 0, (stride, run, sid, bad[:10], arr[bad[:10]], want[bad[:10]])
+    if stride >= 0:
+        assert sparse_runs >= 10
+    if stride == 0:
+        assert lookups[0] < 0.8 * lookups[1], lookups      # fewer table lookups than the dense pass makes

@@ -666,7 +666,10 @@ int nm_workspace_search(nm_workspace *ws, uint64_t num_kmers, int mode, const ui
   P.seg_len = (uint32_t)ws->seg_len;
   P.num_kmers = (uint32_t)num_kmers;
   P.kmin = kmin;
-  P.kmax = kmax;
+  // No k-mer is longer than the segment, so the chains never need to go deeper than that: with the bound clamped the
+  // sums the certificate pass forms (kmax + group size, L + dt) stay far below 2^32 for any --search-range upper end.
+  // (The nominal lengths of a k list, the output width and the reference's query trajectory use the values given.)
+  P.kmax = (uint32_t)std::min<uint64_t>(kmax, std::max<uint64_t>(ws->seg_len, kmin));
   P.nk = nk;
   P.initial = initial_search_length;
   P.mode = mode;

@@ -42,8 +42,8 @@ DEVICE_PIPELINE_DEPTH = int(os.environ.get("NEWMAP_B200_DEVICE_PIPELINE", "4"))
 WRITER_THREADS = int(os.environ.get("NEWMAP_B200_WRITERS", "8"))   # threads writing <id>.unique.uintN windows (pwrite)
 READER_THREADS = int(os.environ.get("NEWMAP_B200_READERS", "0"))   # threads reading the FASTA text into pinned staging (0 = library default)
 # "device": the FASTA text is parsed on the GPU (nm_fasta_*) and segments are searched where they lie;
-# "host": newmap_b200/fasta.py cuts the segments and every segment is uploaded.  Default: device unless --verbose
-# (the per-sequence statistics of the verbose log need the segment bytes on the host).
+# "host": newmap_b200/fasta.py cuts the segments and every segment is uploaded.  Default: device (with --verbose too:
+# the per-sequence statistics of the verbose log are a reduction on the device, NM_OPT_OUT_STATS).
 INGEST = os.environ.get("NEWMAP_B200_INGEST", "auto")
 # [(phase name, seconds since the start of the run)] of the last device-ingest run of this process (bench.py reads it)
 LAST_RUN_TRACE: list = []
@@ -302,7 +302,7 @@ def write_unique_counts(config: SearchConfig):
     ix = open_index(config.fmindex_filepaths[0], config.device)
     lookahead_length = max_kmer_length - 1
     requested_sequence_length = config.kmer_batch_size + lookahead_length
-    if INGEST == "device" or (INGEST == "auto" and not config.verbose):
+    if INGEST in ("device", "auto"):
         if _write_unique_counts_device(config, ix, data_type, unique_count_suffix):
             return
     slots: list[_Slot] = []
@@ -315,7 +315,9 @@ def write_unique_counts(config: SearchConfig):
     if not 0 <= config.rank < config.world_size:
         raise ValueError("rank must be in [0, world_size)")
     segment_number = -1          # running number over all processed segments: the sharding key
-    segment_in_sequence = 0      # window number inside the current sequence: the file offset key
+    file_offset = 0              # positions already emitted into the current file (records that follow one another
+                                 # with the same id are appended to one file, search.py:268-357)
+    last_window_mine = False     # this rank searched the last window emitted into the current file
 
     def finish(slot: _Slot):
         seg, num_kmers, fh, offset = slot.job
@@ -337,13 +339,19 @@ def write_unique_counts(config: SearchConfig):
         # every segment lands at window_number * batch of <id>.unique.uintN (host-side gather: ranks share
         # the files, nothing is exchanged between GPUs); with one rank this is the reference's append
         os.pwrite(fh.fileno(), res.tobytes(), offset * data_type.itemsize)
-        if seg.epilogue:
-            os.ftruncate(fh.fileno(), (offset + num_kmers) * data_type.itemsize)
         slot.job = None
 
     def drain():
         while inflight:
             finish(inflight.popleft())
+
+    def close_current_file():
+        # several ranks share the file and nobody truncated it at open: the rank that searched its last window sets
+        # the size (the other ranks' windows all lie below it, whenever they are written)
+        if current_file is not None:
+            if sharded and last_window_mine:
+                os.ftruncate(current_file.fileno(), file_offset * data_type.itemsize)
+            current_file.close()
 
     with ExitStack() as stack:
         fasta_file = stack.enter_context(optional_gzip_open(config.fasta_filepaths[0], "rb"))
@@ -362,22 +370,22 @@ def write_unique_counts(config: SearchConfig):
                 current_sequence_id = segment.id
                 path = config.output_directory / UNIQUE_COUNT_FILENAME_FORMAT.format(
                     segment.id.decode(), unique_count_suffix)
-                if current_file is not None:
-                    current_file.close()
+                close_current_file()
                 # one rank: truncate like search.py:305.  Several ranks share the file: create without truncating
-                # (another rank may already have written its windows); the rank that owns the epilogue sets the size.
+                # (another rank may already have written its windows); see close_current_file.
                 if sharded:
                     fd = os.open(path, os.O_RDWR | os.O_CREAT, 0o644)
-                    current_file = stack.enter_context(os.fdopen(fd, "r+b"))
+                    current_file = os.fdopen(fd, "r+b")
                 else:
-                    current_file = stack.enter_context(open(path, "wb"))
-                segment_in_sequence = 0
+                    current_file = open(path, "wb")
+                file_offset = 0
                 config.log("Writing unique lengths for sequence ID: {}".format(segment.id.decode()))
             num_kmers = get_num_kmers(segment, max_kmer_length)
             segment_number += 1
-            offset = segment_in_sequence * config.kmer_batch_size
-            segment_in_sequence += 1
-            if segment_number % config.world_size != config.rank:
+            offset = file_offset
+            file_offset += num_kmers
+            last_window_mine = segment_number % config.world_size == config.rank
+            if not last_window_mine:
                 continue
             config.log("Processing {} k-mers".format(num_kmers))
             if len(inflight) >= PIPELINE_DEPTH:
@@ -395,6 +403,8 @@ def write_unique_counts(config: SearchConfig):
             slot.ws.download(slot.out.ptr)
             inflight.append(slot)
         drain()
+        close_current_file()
+        current_file = None
         print_summary_statisitcs(config, current_sequence_id, totals["unique"], totals["ambiguous"],
                                  totals["none"], totals["max_len"], totals["min_len"])
     if not sequence_processed:
@@ -529,11 +539,17 @@ def _write_unique_counts_device(config: SearchConfig, ix: _lib.Index, data_type,
             raise ValueError("rank must be in [0, world_size)")
         inflight: deque = deque()
         files: list = []
-        sequence_processed = False
         current_sequence_id = None
         current_fd = -1
         segment_number = -1
-        segment_in_sequence = 0
+        # --verbose: the log lines come in the reference's order (a segment is finished before the next one is
+        # announced) and the statistics of search.py:318-347 come from a reduction on the device
+        depth = 1 if config.verbose else DEVICE_PIPELINE_DEPTH
+        min_kmer_length = min(config.kmer_lengths)
+        totals = dict(ambiguous=0, unique=0, none=0, max_len=min_kmer_length, min_len=max_kmer_length)
+        if config.verbose:
+            for s_ in slots:
+                s_.ws.option("out_stats", 1)
 
         def write_out(slot, fd, nbytes, offset, truncate_to):
             os.pwrite(fd, memoryview(slot.out.array)[:nbytes], offset)
@@ -541,41 +557,83 @@ def _write_unique_counts_device(config: SearchConfig, ix: _lib.Index, data_type,
                 os.ftruncate(fd, truncate_to)
 
         def finish(slot):
-            (seq_off, seg_len, num_kmers, fd, offset, epilogue) = slot.job
+            (seq_off, seg_len, num_kmers, fd, offset, last_of_file) = slot.job
             st = slot.ws.sync()
             if st.zero_pos >= 0:
                 _raise_zero_count(fa.read(seq_off, seg_len), st)
+            if config.verbose:
+                unique, ambiguous = int(st.unique_positions), int(st.ambiguous_positions)
+                totals["ambiguous"] += ambiguous
+                totals["unique"] += unique
+                totals["none"] += num_kmers - unique - ambiguous
+                if unique:
+                    totals["max_len"] = max(totals["max_len"], int(st.max_unique))
+                    totals["min_len"] = min(totals["min_len"], int(st.min_unique))
+                else:
+                    config.log("No unique lengths found for this sequence segment")
             slot.pending = pool.submit(write_out, slot, fd, num_kmers * itemsize, offset * itemsize,
-                                       (offset + num_kmers) * itemsize if epilogue else None)
+                                       (offset + num_kmers) * itemsize if last_of_file else None)
             slot.job = None
+
+        # the plan: consecutive records with the same id share one file and are APPENDED to it (search.py:268-357 opens
+        # a file anew only when the id changes); a window lands where the windows before it in that file end
+        groups: list = []           # [id, [(sequence offset, length, num_kmers, file offset, epilogue, running number)], size]
+        previous_id = None
+        for header, rec_off, rec_len in fa.records:
+            tokens = header.split()
+            seq_id = tokens[0][1:] if tokens else b""       # fasta.py:60-75
+            if rec_len == 0:
+                continue
+            if previous_id != seq_id:
+                if config.include_sequence_ids or config.exclude_sequence_ids:   # search.py:268-278, quirk included
+                    if (seq_id not in config.include_sequence_ids) or (seq_id in config.exclude_sequence_ids):
+                        continue
+                previous_id = seq_id
+                groups.append([seq_id, [], 0])
+            g = groups[-1]
+            for start, length, epilogue in window_plan(rec_len, requested_sequence_length, lookahead_length):
+                num_kmers = length if epilogue else length - lookahead_length
+                segment_number += 1
+                g[1].append((rec_off + start, length, num_kmers, g[2], epilogue, segment_number))
+                g[2] += num_kmers
+        sequence_processed = bool(groups)
+        seen_paths: set = set()
 
         with ThreadPoolExecutor(max_workers=max(1, WRITER_THREADS)) as pool:
             try:
-                for header, rec_off, rec_len in fa.records:
-                    tokens = header.split()
-                    seq_id = tokens[0][1:] if tokens else b""       # fasta.py:60-75
-                    if rec_len == 0:
-                        continue
-                    if current_sequence_id != seq_id:
-                        if config.include_sequence_ids or config.exclude_sequence_ids:   # search.py:268-278, quirk included
-                            if (seq_id not in config.include_sequence_ids) or (seq_id in config.exclude_sequence_ids):
-                                continue
-                        sequence_processed = True
-                        current_sequence_id = seq_id
-                        out_path = config.output_directory / UNIQUE_COUNT_FILENAME_FORMAT.format(
-                            seq_id.decode(), unique_count_suffix)
-                        flags = os.O_RDWR | os.O_CREAT | (0 if sharded else os.O_TRUNC)
-                        current_fd = os.open(out_path, flags, 0o644)
-                        files.append(current_fd)
-                        segment_in_sequence = 0
-                    for start, length, epilogue in window_plan(rec_len, requested_sequence_length, lookahead_length):
-                        num_kmers = length if epilogue else length - lookahead_length
-                        segment_number += 1
-                        offset = segment_in_sequence * config.kmer_batch_size
-                        segment_in_sequence += 1
-                        if segment_number % config.world_size != config.rank:
+                for seq_id, wins, total in groups:
+                    if config.verbose:
+                        while inflight:
+                            finish(inflight.popleft())
+                        print_summary_statisitcs(config, current_sequence_id or b"", totals["unique"],
+                                                 totals["ambiguous"], totals["none"], totals["max_len"],
+                                                 totals["min_len"])
+                    current_sequence_id = seq_id
+                    out_path = config.output_directory / UNIQUE_COUNT_FILENAME_FORMAT.format(
+                        seq_id.decode(), unique_count_suffix)
+                    if out_path in seen_paths:
+                        # the id came back after another one: the reference truncates the file and starts again
+                        if sharded:
+                            raise ValueError(f"sequence id {seq_id.decode()!r} appears again after another sequence: "
+                                             "not supported when the run is sharded over several ranks")
+                        while inflight:
+                            finish(inflight.popleft())
+                        for s_ in slots:
+                            if s_.pending is not None:
+                                s_.pending.result()
+                                s_.pending = None
+                    seen_paths.add(out_path)
+                    # one rank: truncate like search.py:305.  Several ranks share the file: create without truncating
+                    # (another rank may already have written its windows); the owner of the last window sets the size.
+                    flags = os.O_RDWR | os.O_CREAT | (0 if sharded else os.O_TRUNC)
+                    current_fd = os.open(out_path, flags, 0o644)
+                    files.append(current_fd)
+                    config.log("Writing unique lengths for sequence ID: {}".format(seq_id.decode()))
+                    for n_win, (seq_off, length, num_kmers, offset, epilogue, number) in enumerate(wins):
+                        if number % config.world_size != config.rank:
                             continue
-                        if len(inflight) >= DEVICE_PIPELINE_DEPTH:
+                        config.log("Processing {} k-mers".format(num_kmers))
+                        if len(inflight) >= depth:
                             finish(inflight.popleft())
                         slot = next((s for s in slots if s.job is None and (s.pending is None or s.pending.done())), None)
                         if slot is None:
@@ -583,8 +641,8 @@ def _write_unique_counts_device(config: SearchConfig, ix: _lib.Index, data_type,
                         if slot.pending is not None:
                             slot.pending.result()
                             slot.pending = None
-                        slot.job = (rec_off + start, length, num_kmers, current_fd, offset, epilogue)
-                        slot.ws.attach(fa, rec_off + start, length)
+                        slot.job = (seq_off, length, num_kmers, current_fd, offset, n_win == len(wins) - 1)
+                        slot.ws.attach(fa, seq_off, length)
                         slot.ws.search(num_kmers, config.kmer_lengths, config.is_binary_search,
                                        config.initial_search_length, config.use_reverse_complement, config.algorithm,
                                        itemsize)
@@ -594,6 +652,9 @@ def _write_unique_counts_device(config: SearchConfig, ix: _lib.Index, data_type,
                 while inflight:
                     finish(inflight.popleft())
                 mark("all_segments_searched")
+                if config.verbose:
+                    print_summary_statisitcs(config, current_sequence_id or b"", totals["unique"], totals["ambiguous"],
+                                             totals["none"], totals["max_len"], totals["min_len"])
                 for s_ in slots:
                     if s_.pending is not None:
                         s_.pending.result()

@@ -20,7 +20,7 @@ def test_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(L, n), n
     assert sorted(_lib.SIGNATURES) == names
-    assert L.nm_abi_version() == 2
+    assert L.nm_abi_version() == 3
     assert L.nm_strerror(-2).decode() == "not a valid .awfmi index"
 
 

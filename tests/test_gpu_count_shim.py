@@ -65,10 +65,12 @@ def test_shim_against_the_reference_extension_call_for_call():
     ref = ora.ref_modules()[0]
     seq = b"AAAAATTTTTATCGAATCGA"
     for ix in (str(GOLD / "genome_s1.awfmi"), str(GOLD / "genome_s3.awfmi"), str(GOLD / "quirk_s4.awfmi")):
-        for args in ((seq, [0], [-1]), (seq, [-1], [2]), (b"AAAA", [0], [0]), (b"AAAA", [3], [2]), ("AAAA", [0], [2]),
+        # (a zero-length k-mer is answered 0 by the reference on a seed-length-1 index and is undefined behaviour -- it
+        #  reads kmer[-1] -- on any other, so it is not compared live; test_zero_length_kmers_count_zero pins the shim)
+        for args in ((seq, [0], [-1]), (seq, [-1], [2]), (b"AAAA", [3], [2]), ("AAAA", [0], [2]),
                      (b"AAAA", (0,), [2]), (b"AAAA", [0], (2,)), (b"AAAA", [0], [2.0]), (b"AAAA", [0, 1], [2]),
-                     (bytearray(b"AAAA"), [0], [2]), (seq, [0, 4, 9], [4, 2, 3]), (seq, [0, 1, 2, 5], [0, 20, 3, 15]),
-                     (b"NNNNACGTnnacgtRYKM", [0, 4, 3, 8, 14], [4, 4, 6, 6, 4]), (seq, [], []), (seq, [20], [0])):
+                     (bytearray(b"AAAA"), [0], [2]), (seq, [0, 4, 9], [4, 2, 3]), (seq, [0, 1, 2, 5], [7, 19, 3, 15]),
+                     (b"NNNNACGTnnacgtRYKM", [0, 4, 3, 8, 14], [4, 4, 6, 6, 4]), (seq, [], [])):
             for threads in (1, 0, 255, 256, -1, 1.5, True):
                 a = _outcome(ref.count_kmers_from_sequence, ix, *args, threads)
                 b = _outcome(shim.count_kmers_from_sequence, ix, *args, threads)
@@ -79,6 +81,14 @@ def test_shim_against_the_reference_extension_call_for_call():
                 a = _outcome(ref.count_kmers, ix, kmers, threads)
                 b = _outcome(shim.count_kmers, ix, kmers, threads)
                 assert a == b, (ix, kmers, threads, a, b)
+
+
+def test_zero_length_kmers_count_zero():
+    from newmap_b200 import count as shim
+    ix = str(GOLD / "genome_s1.awfmi")      # seed length 1: the one index on which the reference defines this (-> 0)
+    assert shim.count_kmers_from_sequence(ix, b"AAAA", [0, 1, 4], [0, 2, 0], 1) == [0, 14, 0]
+    if ora.ref_available():
+        assert ora.ref_modules()[0].count_kmers_from_sequence(ix, b"AAAA", [0, 1, 4], [0, 2, 0], 1) == [0, 14, 0]
 
 
 def test_reference_host_loop_on_the_shim_reproduces_reference_files(manifest, golden_searches):

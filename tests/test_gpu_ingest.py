@@ -147,3 +147,46 @@ def test_device_ingest_gz_filters_and_sharding(nm, tmp_path, monkeypatch):
         S.write_unique_counts(S.SearchConfig(fasta_filepaths=[GOLD / "quirk.fa"], fmindex_filepaths=[GOLD / "quirk_s6.awfmi"],
                                              output_directory=out, rank=rank, world_size=2, **kw))
     assert {p.name: p.read_bytes() for p in sorted(out.iterdir())} == a
+
+
+@pytest.mark.parametrize("ingest", ["host", "device"])
+def test_records_that_repeat_an_id_like_the_reference(nm, tmp_path, monkeypatch, ingest):
+    """tests/golden/dup_*.fa (oracle/gen_dup_golden.py): an id twice in a row is APPENDED to one file
+    (search.py:268-357 opens a file anew only when the id changes), an id that comes back after another one truncates
+    it -- both paths write what the unmodified reference wrote, also when two ranks share the files."""
+    gold = np.load(GOLD / "dup_ids.npz")
+    runs = [dict(kmer_lengths=list(range(20, 61)), is_binary_search=True, kmer_batch_size=1000),
+            dict(kmer_lengths=[22, 30, 45], is_binary_search=False, kmer_batch_size=700)]
+    for tag in ("append", "return"):
+        for n, kw in enumerate(runs):
+            got = _run_search(tmp_path, f"{tag}{n}", GOLD / f"dup_{tag}.fa", GOLD / f"dup_{tag}.awfmi", ingest, monkeypatch, **kw)
+            assert sorted(got) == ["a.unique.uint8", "b.unique.uint8"]
+            for sid in ("a", "b"):
+                want = gold[f"{tag}|run{n}|{sid}"]
+                assert np.array_equal(np.frombuffer(got[f"{sid}.unique.uint8"], dtype=np.uint8), want), (tag, n, sid, ingest)
+    # sharded over two ranks (files pre-filled with stale bytes longer than the result: the size is set by the owner
+    # of a file's last window)
+    from newmap_b200 import search as S
+    out = tmp_path / f"sharded_{ingest}"
+    out.mkdir()
+    for sid in ("a", "b"):
+        (out / f"{sid}.unique.uint8").write_bytes(b"\xff" * 9000)
+    monkeypatch.setattr(S, "INGEST", ingest)
+    for rank in (1, 0):
+        S.write_unique_counts(S.SearchConfig(fasta_filepaths=[GOLD / "dup_append.fa"], fmindex_filepaths=[GOLD / "dup_append.awfmi"],
+                                             output_directory=out, rank=rank, world_size=2, **runs[0]))
+    for sid in ("a", "b"):
+        assert np.array_equal(np.fromfile(out / f"{sid}.unique.uint8", dtype=np.uint8), gold[f"append|run0|{sid}"]), sid
+
+
+def test_verbose_statistics_come_from_the_device(nm, tmp_path, monkeypatch, capsys):
+    """--verbose no longer drops to the host reader: the per-sequence summary (search.py:885-902) is reduced on the
+    device (NM_OPT_OUT_STATS) and equals the one the host path computes from the bytes."""
+    logs = {}
+    for ingest in ("host", "device"):
+        capsys.readouterr()
+        _run_search(tmp_path, "verbose", GOLD / "quirk.fa", GOLD / "quirk_s6.awfmi", ingest, monkeypatch,
+                    kmer_lengths=list(range(20, 101)), is_binary_search=True, kmer_batch_size=1500, verbose=True)
+        logs[ingest] = capsys.readouterr().err.splitlines()
+    assert logs["host"] == logs["device"]
+    assert any("unique lengths found" in t for t in logs["device"]) and any("Processing 1500 k-mers" in t for t in logs["device"])

@@ -318,11 +318,13 @@ def test_tuning_options_do_not_change_results(nm, indexes):
         ws.option("own_chains", (1, 0, 3)[n % 3])
         ws.option("stall", (2, 0, 1, 5, 3)[n % 5])
         ws.option("cert_runs", (0, 1, 2, 7)[n % 4])
-        ws.option("pass1", pass1)     # first-pass kernel: tiled with lane refill / one thread per position
+        ws.option("pass1", pass1)     # first-pass kernel: sparse with lane refill / one thread per position
+        ws.option("stride", (0, 1, 2, 3, 5, 8, 4)[n % 7])   # sparse first pass: positions per unconditional table lookup
         ws.upload(buf.ptr, len(seq))
         ws.search(len(seq), kl, True, out_width=1)
         ws.download(out.ptr)
         st = ws.sync()
         assert st.replayed == 0
         assert np.array_equal(out.array[:len(seq)], want), (dcap, gsize, pass1)
+        assert st.stride == (1 if pass1 == 1 else (8, 1, 2, 3, 5, 8, 4)[n % 7]), (n, st.stride)
     ws.close()

@@ -15,9 +15,13 @@ from newmap_b200 import _lib  # noqa: E402
 workload = sys.argv[1] if len(sys.argv) > 1 else "c3_1g"
 first = int(sys.argv[2]) if len(sys.argv) > 2 else 0
 fa, ixp = bench.prepare_workload(workload)
-segs, total = bench.load_segments(fa, first, 1)
+from newmap_b200.fasta import sequence_segments  # noqa: E402
+from newmap_b200.search import get_num_kmers  # noqa: E402
+with open(fa, "rb") as fh:
+    every = [(s, get_num_kmers(s, bench.K_RANGE[1])) for s in sequence_segments(fh, bench.BATCH + bench.K_RANGE[1] - 1, bench.K_RANGE[1] - 1)]
+total = len(every)
 count = int(sys.argv[3]) if len(sys.argv) > 3 else total
-segs, total = bench.load_segments(fa, first, count)
+segs = every[first:first + count]
 ix = _lib.Index(ixp, device=0)
 cap = max(len(s.data) for s, _ in segs)
 ws = _lib.Workspace(ix, cap)

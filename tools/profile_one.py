@@ -13,8 +13,7 @@ workload = sys.argv[1] if len(sys.argv) > 1 else "c2_100m"
 repeats = int(sys.argv[2]) if len(sys.argv) > 2 else 3
 algo = sys.argv[3] if len(sys.argv) > 3 else "auto"
 fa, ixp = bench.prepare_workload(workload)
-(segs, total) = bench.load_segments(fa, 1, 1)
-seg, n = segs[0]
+seg, n = bench.sample_segment(fa, 1)
 ix = _lib.Index(ixp, device=0)
 ws = _lib.Workspace(ix, len(seg.data))
 pb = _lib.PinnedBuffer(len(seg.data))
@@ -24,4 +23,4 @@ kl = list(range(20, 201))
 for _ in range(repeats):
     ws.search(n, kl, True, algo=algo, out_width=1)
     st = ws.sync()
-print({k: v for k, v in st.as_dict().items() if k.startswith("ms_") or k.endswith("steps") or k == "generic_searches"})
+print({k: v for k, v in st.as_dict().items() if k.startswith("ms_") or "steps" in k or "lookups" in k or k in ("generic_searches", "stride", "launches")})

@@ -164,6 +164,10 @@ int nm_workspace_sync(nm_workspace *ws, nm_stats *stats);
                              between the table depth and the shortest length allows (at most 8), 1 = every window */
 #define NM_OPT_OUT_STATS 10 /* 1: one more reduction over the output fills stats.unique_positions, ambiguous_positions,
                              min_unique, max_unique (what `newmap search --verbose` prints per sequence); default 0 */
+#define NM_OPT_SUBDEPTH 11 /* a range that starts below the depth of the derived seed table but reaches it (12:255 on the 16-letter
+                             table): 0 (default) = chains start from the derived table and the lengths below its depth are
+                             settled with exact counts for the few positions the table does not rule out; 1 = the whole
+                             search falls back to the file's own table */
 int nm_workspace_option(nm_workspace *ws, int option, uint64_t value);
 /* 64-bit FNV-style checksum of the last search's output computed on the device (for
  * device-resident runs that never copy the output back). */

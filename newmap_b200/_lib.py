@@ -290,10 +290,10 @@ class Workspace:
             pass
 
     def option(self, name: str, value: int):
-        """'ref_lf' | 'dcap' | 'gsize' | 'pass1' | 'gsize2' | 'own_chains' | 'stall' | 'cert_runs' | 'stride' | 'out_stats'
+        """'ref_lf' | 'dcap' | 'gsize' | 'pass1' | 'gsize2' | 'own_chains' | 'stall' | 'cert_runs' | 'stride' | 'out_stats' | 'subdepth'
         (NM_OPT_*): instrumentation / tuning, never changes results."""
         check(load().nm_workspace_option(self._h, {"ref_lf": 1, "dcap": 2, "gsize": 3, "pass1": 4, "gsize2": 5, "own_chains": 6,
-                                                   "stall": 7, "cert_runs": 8, "stride": 9, "out_stats": 10}[name], int(value)),
+                                                   "stall": 7, "cert_runs": 8, "stride": 9, "out_stats": 10, "subdepth": 11}[name], int(value)),
               "nm_workspace_option")
 
     def attach(self, fasta: "Fasta", seq_offset: int, seg_len: int):

@@ -367,6 +367,10 @@ struct SegParams {
   unsigned long long *counters;  // CTR_N slots
   uint32_t seg_len, num_kmers;
   uint32_t kmin, kmax, nk, initial;
+  uint32_t keff;         // shortest length the trajectory-free passes work with: max(kmin, sl).  When kmin < sl (a range that
+                         // starts below the depth of the seed table) the lengths kmin .. sl-1 are settled by resolve_thread
+                         // with exact counts, for the few positions the table does not rule out (`sub`)
+  uint8_t *sub;          // seg_len (only when keff > kmin): 1 = the sl-1 letters starting here may be unique (subdepth_candidate)
   int mode;       // 0 range, 1 list
   int use_rc;
   int out_width;  // 1, 2, 4
@@ -813,6 +817,23 @@ NM_HD void free_chain_thread(const DevIndex &ix, const uint32_t *C32, const SegP
 // Stored bounds are valid upper bounds <= kmin, so the later passes (which only rewrite kDeep entries and use
 // G[e-1] + 1 / R[i+1] + 1 as upper bounds themselves) need no change.
 // ---------------------------------------------------------------------------------------------
+// Lengths below the depth of the table (a search range that starts at kmin < sl, e.g. 12:255 on the 16-letter table).
+// The count is non-increasing in the length, so a position can only have an answer below sl when it is unique at sl
+// itself; and the 4 table entries that share the first sl-1 letters of the window (keys 4x .. 4x+3: one aligned 64-byte
+// group, which the memory system fetches whole anyway) give a LOWER bound on the two-strand count of those sl-1
+// letters: the occurrences followed (forward strand) / preceded (other strand) by a regular letter.  A bound >= 2
+// rules the position out; the rest (a few per cent in a genome of 4^(sl-1) letters or more) gets exact counts.
+NM_HD bool subdepth_candidate(const SegParams &P, uint32_t q) {
+  const uint32_t key = window_key(P, q) & ~3u;
+  uint32_t lb = 0;
+  for (uint32_t c = 0; c < 4u; ++c) {
+    const SeedEntryPair e = P.seedpair[key + c];
+    lb += e.fwd.len + (P.use_rc ? e.rc.len : 0u);
+    if (lb > 1u) return false;
+  }
+  return true;
+}
+
 constexpr uint32_t kMaxStride = 8;
 // stride chosen when none is asked for: as wide as the slack between the table depth and the shortest length allows
 NM_HD uint32_t sparse_auto_stride(uint32_t kmin, uint32_t sl, bool pair_table, uint32_t asked) {
@@ -824,7 +845,7 @@ NM_HD uint32_t sparse_auto_stride(uint32_t kmin, uint32_t sl, bool pair_table, u
 }
 NM_HD bool sparse_numeric(const SegParams &P, uint32_t v) { return v >= 1u && v <= P.kmax; }
 NM_HD bool sparse_exact_only_end(const SegParams &P, uint32_t e) { return P.mode == 1 && e == P.seg_len; }
-NM_HD bool sparse_exact_only_start(const SegParams &P, uint32_t i) { return P.mode == 1 && P.seg_len - i < P.kmin; }
+NM_HD bool sparse_exact_only_start(const SegParams &P, uint32_t i) { return P.mode == 1 && P.seg_len - i < P.keff; }
 
 // ends are grouped [0, head), [head, head + S), ... with head = sl + S - 1: the window of sl letters that starts at
 // q = c * S + (S - 1) ends at the first end of cell c and starts at the last start of cell c (starts [c*S, c*S + S))
@@ -855,14 +876,14 @@ NM_HD bool sparse_next_rc(const SegParams &P, uint32_t first, uint32_t &end1) {
 NM_HD uint32_t sparse_spread_fwd(const SegParams &P, uint32_t cur, uint32_t last, uint32_t v) {
   uint32_t e = cur + 1u;
   if (!sparse_numeric(P, v)) return e;
-  for (uint32_t b = v + 1u; e <= last && b <= P.kmin && fwd_wanted(P, e) && !sparse_exact_only_end(P, e); ++e, ++b) P.G[e] = b;
+  for (uint32_t b = v + 1u; e <= last && b <= P.keff && fwd_wanted(P, e) && !sparse_exact_only_end(P, e); ++e, ++b) P.G[e] = b;
   return e;
 }
 // R[end1 - 1] = v has just been settled: spread over the starts before it; returns the new end1
 NM_HD uint32_t sparse_spread_rc(const SegParams &P, uint32_t first, uint32_t end1, uint32_t v) {
   uint32_t n = end1 - 1u;   // starts [first, n) remain
   if (!sparse_numeric(P, v)) return n;
-  for (uint32_t b = v + 1u; n > first && b <= P.kmin && rc_wanted(P, n - 1u) && !sparse_exact_only_start(P, n - 1u); --n, ++b)
+  for (uint32_t b = v + 1u; n > first && b <= P.keff && rc_wanted(P, n - 1u) && !sparse_exact_only_start(P, n - 1u); --n, ++b)
     P.R[n - 1u] = b;
   return n;
 }
@@ -1168,15 +1189,16 @@ NM_HD uint64_t ref_trajectory_steps(const SegParams &P, uint32_t sl, uint32_t li
   return total;
 }
 
-NM_HD void resolve_thread(const DevIndex &ix, const SegParams &P, uint32_t i, uint64_t &ref_lf) {
+NM_HD void resolve_thread(const DevIndex &ix, const SegParams &P, uint32_t i, uint64_t &ref_lf, uint32_t &steps) {
   uint32_t ans = 0;
   if (!(P.codes[i] & kNoStart)) {
     const uint32_t r = P.use_rc ? P.R[i] : 0u;
     if (P.mode == 0) {
       const uint32_t lim = length_limit(P, i);
-      if (lim >= P.kmin) {
+      const uint32_t kq = P.keff;                        // == kmin unless the range starts below the table depth
+      if (lim >= kq) {
         if (r != kInf) {
-          const uint32_t k0 = r > P.kmin ? r : P.kmin;
+          const uint32_t k0 = r > kq ? r : kq;
           if (k0 <= lim) {
             if (fwd_unique(P, i, i + k0)) {              // most positions: unique at the shortest length they may have
               ans = k0;
@@ -1191,6 +1213,19 @@ NM_HD void resolve_thread(const DevIndex &ix, const SegParams &P, uint32_t i, ui
           }
         }
         if (P.want_ref_lf) ref_lf += ref_trajectory_steps(P, ix.seed_len, lim, ans, P.use_rc ? r : 0u);
+      }
+      if (P.kmin < kq && lim >= P.kmin) {
+        // lengths kmin .. kq-1, below the table depth: possible only where the position is unique at kq (or cannot
+        // reach kq at all), and not ruled out by the table (subdepth_candidate) -- exact counts with the reference's
+        // own count (count_both) from the longest such length downwards
+        const bool cand = lim < kq ? true : (ans == kq && (P.sub[i] || (P.codes[i] & kSeedBad)));
+        if (cand) {
+          uint32_t k = lim < kq ? lim : kq - 1u;
+          if (count_both(ix, P.seg, i, k, P.use_rc != 0, steps) == 1u) {
+            while (k > P.kmin && count_both(ix, P.seg, i, k - 1u, P.use_rc != 0, steps) == 1u) --k;
+            ans = k;
+          }
+        }
       }
     } else {
       const uint32_t b = next_barrier(P, i);

@@ -267,8 +267,22 @@ __global__ void __launch_bounds__(kBlock, 6) k_pass1_sparse(DevIndex ix, SegPara
     for (int j = 0; j < kSpCells; ++j) {
       ent[j] = make_uint4(0u, 0u, 0u, 0u);
       if (win_ok[j]) {
-        ent[j] = __ldg(reinterpret_cast<const uint4 *>(P.seedpair + key[j]));
+        if (P.sub) {
+          // a range that starts below the table depth (stride 1, q = the start position): the four entries that share
+          // the window's first sl-1 letters, one aligned 64-byte group (subdepth_candidate, nm_core.cuh)
+          const uint4 *grp = reinterpret_cast<const uint4 *>(P.seedpair + (key[j] & ~3u));
+          const uint4 g0 = __ldg(grp), g1 = __ldg(grp + 1), g2 = __ldg(grp + 2), g3 = __ldg(grp + 3);
+          const uint32_t k3 = key[j] & 3u;
+          ent[j] = k3 == 0u ? g0 : k3 == 1u ? g1 : k3 == 2u ? g2 : g3;
+          uint32_t lb = g0.y + g1.y + g2.y + g3.y;
+          if (P.use_rc) lb += g0.w + g1.w + g2.w + g3.w;
+          P.sub[q[j]] = lb <= 1u ? 1 : 0;
+        } else {
+          ent[j] = __ldg(reinterpret_cast<const uint4 *>(P.seedpair + key[j]));
+        }
         ++seeds;
+      } else if (P.sub && q[j] < P.seg_len) {
+        P.sub[q[j]] = 0;
       }
     }
 #pragma unroll
@@ -464,8 +478,10 @@ __global__ void __launch_bounds__(kBlock) k_free_generic(DevIndex ix, SegParams 
 __global__ void __launch_bounds__(kBlock) k_resolve(DevIndex ix, SegParams P) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   uint64_t ref_lf = 0;
-  if (i < P.num_kmers) resolve_thread(ix, P, i, ref_lf);
+  uint32_t steps = 0;
+  if (i < P.num_kmers) resolve_thread(ix, P, i, ref_lf, steps);
   if (P.want_ref_lf) flush_counter64(&P.counters[CTR_REF_LF], ref_lf);
+  if (P.keff > P.kmin) flush_counter(&P.counters[CTR_LF], steps);
 }
 
 // NM_OPT_OUT_STATS: what `newmap search --verbose` reports per sequence (search.py:318-347,885-902), reduced on the device

@@ -58,6 +58,7 @@ struct nm_workspace {
   const uint8_t *seg_ext = nullptr;  // segment attached from a parsed FASTA (nm_workspace_attach) instead of uploaded
   uint32_t *d_pk = nullptr, *d_tile_first = nullptr, *d_G = nullptr, *d_R = nullptr;
   uint64_t *d_barmask = nullptr;
+  uint8_t *d_sub = nullptr;  // candidates for lengths below the table depth (allocated by the first search that needs it)
   void *d_out = nullptr;
   uint32_t *d_klist = nullptr;
   uint32_t klist_cap = 0;
@@ -72,7 +73,7 @@ struct nm_workspace {
   int algo_req = 0, algo_used = 0;
   bool timed_h2d = false, timed_d2h = false;
   void *pending_out = nullptr;
-  uint32_t opt_ref_lf = 0, opt_dcap = 0, opt_gsize = 0, opt_pass1 = 0, opt_gsize2 = ~0u, opt_own_chains = ~0u, opt_stall = ~0u, opt_cert_runs = 0, opt_stride = 0, opt_out_stats = 0;
+  uint32_t opt_ref_lf = 0, opt_dcap = 0, opt_gsize = 0, opt_pass1 = 0, opt_gsize2 = ~0u, opt_own_chains = ~0u, opt_stall = ~0u, opt_cert_runs = 0, opt_stride = 0, opt_out_stats = 0, opt_subdepth = 0;
   // several sequences x several indexes (nm_workspace_multi); cleared by the next upload / attach
   nm::CoarseGroup *d_cgroups = nullptr;  // coarse certificate round: 2 per group of >= kMinGsize2 positions
   uint64_t cgroup_cap = 0;
@@ -531,6 +532,7 @@ void nm_workspace_destroy(nm_workspace *ws) {
   cudaFree(ws->d_codes);
   cudaFree(ws->d_pk);
   cudaFree(ws->d_barmask);
+  cudaFree(ws->d_sub);
   cudaFree(ws->d_tile_first);
   cudaFree(ws->d_G);
   cudaFree(ws->d_R);
@@ -652,6 +654,7 @@ int nm_workspace_search(nm_workspace *ws, uint64_t num_kmers, int mode, const ui
     }
     NM_CUDA(cudaMemcpyAsync(ws->d_klist, klist, (size_t)nk * 4, cudaMemcpyHostToDevice, ws->stream));
   }
+  if (ws->multi_ix) algo = NM_ALGO_TRAJECTORY;  // the summed count is searched on the reference's own trajectory
   nm::SegParams &P = ws->P;
   P.seg = ws->seg_ext ? ws->seg_ext : ws->d_seg;
   P.codes = ws->d_codes;
@@ -680,11 +683,21 @@ int nm_workspace_search(nm_workspace *ws, uint64_t num_kmers, int mode, const ui
     // chains start from the deeper derived table when every queried length reaches its depth; the estimate of the
     // reference's LF steps (NM_OPT_REF_LF) needs thresholds exact down to the index's own seed length
     const nm::DevIndex &dv = ws->ix->dev;
-    const bool deep = dv.seedx && kmin >= dv.seedx_len && ws->opt_ref_lf != 2u;
+    // ... or, for a RANGE that starts below its depth but reaches it (12:255 on the 16-letter table), when the lengths
+    // below the depth are settled separately (P.keff, resolve_thread): NM_OPT_SUBDEPTH 1 switches that off
+    const bool sub = dv.seedx && mode == NM_MODE_RANGE && kmin < dv.seedx_len && kmax >= dv.seedx_len &&
+                     kmin >= dv.seed_len && ws->opt_subdepth == 0u && ws->opt_ref_lf != 2u && algo == NM_ALGO_AUTO;
+    const bool deep = dv.seedx && (kmin >= dv.seedx_len || sub) && ws->opt_ref_lf != 2u;
     P.want_ref_lf = (ws->opt_ref_lf && !deep) ? 1 : 0;
     P.sl = deep ? dv.seedx_len : dv.seed_len;
     P.seedtab = deep ? nullptr : dv.seed32;
     P.seedpair = deep ? dv.seedx : nullptr;
+    P.keff = sub ? dv.seedx_len : kmin;
+    P.sub = nullptr;
+    if (sub) {
+      if (!ws->d_sub) NM_CUDA(cudaMalloc((void **)&ws->d_sub, ws->max_seg_len + 16));
+      P.sub = ws->d_sub;
+    }
     const uint32_t sl = P.sl;
     P.dcap = ws->opt_dcap ? ws->opt_dcap : (deep ? sl + 8 : sl + 12);
     if (P.dcap <= sl) P.dcap = sl + 1;
@@ -696,9 +709,8 @@ int nm_workspace_search(nm_workspace *ws, uint64_t num_kmers, int mode, const ui
     // walk the same rank blocks, L2 hits) and the later passes pay more than it saves (8.45 -> 8.03 G positions/s).
     P.stall = P.dcap < kmax ? (ws->opt_stall == ~0u ? 0u : ws->opt_stall) : 0u;
     // sparse first pass (nm_core.cuh): one window per `stride` positions, the rest settled by bounds spread from it
-    P.stride = nm::sparse_auto_stride(kmin, sl, deep, ws->opt_stride);
+    P.stride = nm::sparse_auto_stride(P.keff, sl, deep, ws->opt_stride);
   }
-  if (ws->multi_ix) algo = NM_ALGO_TRAJECTORY;  // the summed count is searched on the reference's own trajectory
   ws->algo_req = algo;
   ws->have_search = true;
   ws->timed_d2h = false;
@@ -815,6 +827,7 @@ int nm_workspace_option(nm_workspace *ws, int option, uint64_t value) {
     case NM_OPT_STALL: if (value > 64) return NM_EARG; ws->opt_stall = (uint32_t)value; return NM_OK;
     case NM_OPT_CERT_RUNS: if (value > 64) return NM_EARG; ws->opt_cert_runs = (uint32_t)value; return NM_OK;
     case NM_OPT_GSIZE2: if (value > 65536) return NM_EARG; ws->opt_gsize2 = (uint32_t)value; return NM_OK;
+    case NM_OPT_SUBDEPTH: ws->opt_subdepth = value ? 1u : 0u; return NM_OK;
     case NM_OPT_OUT_STATS: ws->opt_out_stats = value ? 1u : 0u; return NM_OK;
     case NM_OPT_STRIDE: if (value > nm::kMaxStride) return NM_EARG; ws->opt_stride = (uint32_t)value; return NM_OK;
     default: return NM_EARG;

@@ -121,7 +121,14 @@ int emu_min_unique(EmuIndex *ix, const uint8_t *seg, uint32_t seg_len, uint32_t 
   else { P.kmin = P.kmax = klist[0]; for (uint32_t j = 0; j < nk; ++j) { if (klist[j] < P.kmin) P.kmin = klist[j]; if (klist[j] > P.kmax) P.kmax = klist[j]; } }
   // nm_lib.cu nm_workspace_search: the deeper table when every queried length reaches its depth (the estimate of the
   // reference's LF steps is then off, so it is only requested on the index's own table)
-  const bool deep = ix->dev.seedx && P.kmin >= ix->dev.seedx_len;
+  // ... or (nm_lib.cu) a range that starts below its depth but reaches it, the lengths below settled by resolve_thread
+  const bool sub = ix->dev.seedx && mode == 0 && P.kmin < ix->dev.seedx_len && P.kmax >= ix->dev.seedx_len &&
+                   P.kmin >= ix->dev.seed_len && algo == 0 && !(stride & 0x40000000u);
+  if (stride != 0xFFFFFFFFu) stride &= ~0x40000000u;     // bit 30 of the stride argument: NM_OPT_SUBDEPTH 1
+  const bool deep = ix->dev.seedx && (P.kmin >= ix->dev.seedx_len || sub);
+  std::vector<uint8_t> subv(sub ? seg_len + 16 : 0);
+  P.keff = sub ? ix->dev.seedx_len : P.kmin;
+  P.sub = sub ? subv.data() : nullptr;
   P.sl = deep ? ix->dev.seedx_len : ix->dev.seed_len;
   P.seedtab = deep ? nullptr : ix->dev.seed32;
   P.seedpair = deep ? ix->dev.seedx : nullptr;
@@ -129,7 +136,7 @@ int emu_min_unique(EmuIndex *ix, const uint8_t *seg, uint32_t seg_len, uint32_t 
   P.dcap = dcap ? dcap : P.sl + 12; if (P.dcap <= P.sl) P.dcap = P.sl + 1;
   P.stall = P.dcap < P.kmax ? stall : 0;
   // nm_lib.cu: 0 = the widest stride the slack allows; 0xFFFFFFFF = the dense thread-per-position first pass
-  P.stride = stride == 0xFFFFFFFFu ? 1u : sparse_auto_stride(P.kmin, P.sl, deep, stride);
+  P.stride = stride == 0xFFFFFFFFu ? 1u : sparse_auto_stride(P.keff, P.sl, deep, stride);
   for (uint32_t p = 0; p < seg_len; ++p) prep_thread(ix->dev, P, p);
   for (uint32_t w = 0; w < seg_len / 16 + 2; ++w) pack_thread(P, w);
   const uint32_t ntiles = (seg_len + kTile - 1) / kTile;
@@ -142,6 +149,8 @@ int emu_min_unique(EmuIndex *ix, const uint8_t *seg, uint32_t seg_len, uint32_t 
     const bool fast = (algo != 2) && ix->has_rank32 && P.kmin >= ix->dev.seed_len;
     P.fast = fast;
     if (fast) {
+      if (sub)   // k_pass1_sparse phase A: which starts the table does not rule out for the lengths below its depth
+        for (uint32_t q = 0; q < seg_len; ++q) subv[q] = !(codes[q] & kSeedBad) && subdepth_candidate(P, q);
       if (deep && stride != 0xFFFFFFFFu) sparse_pass1_serial(ix->dev, ix->c32, P, steps, seeds);   // k_pass1_sparse
       else for (uint32_t p = 0; p <= seg_len; ++p) free_chain_thread(ix->dev, ix->c32, P, p, true, steps, seeds);
       if (P.dcap < P.kmax) {
@@ -165,7 +174,7 @@ int emu_min_unique(EmuIndex *ix, const uint8_t *seg, uint32_t seg_len, uint32_t 
     } else {
       for (uint32_t p = 0; p <= seg_len; ++p) free_generic_thread(ix->dev, P, p, true, steps, ns);
     }
-    for (uint32_t i = 0; i < num_kmers; ++i) resolve_thread(ix->dev, P, i, ref_lf);
+    for (uint32_t i = 0; i < num_kmers; ++i) resolve_thread(ix->dev, P, i, ref_lf, steps);
   }
   if (stats) {
     stats[0] = steps; stats[1] = nq; stats[2] = ns; stats[3] = (int64_t)ctr[CTR_ANOMALY];
@@ -197,7 +206,7 @@ int emu_min_unique_multi(EmuIndex *const *ixs, uint32_t n_ix, const uint8_t *con
   if (mode == 0) { P.kmin = klist[0]; P.kmax = klist[1]; }
   else { P.kmin = P.kmax = klist[0]; for (uint32_t j = 0; j < nk; ++j) { if (klist[j] < P.kmin) P.kmin = klist[j]; if (klist[j] > P.kmax) P.kmax = klist[j]; } }
   const DevIndex &d0 = ixs[0]->dev;
-  P.sl = d0.seed_len; P.seedtab = d0.seed32; P.seedpair = nullptr; P.dcap = P.sl + 12; P.stride = 1;
+  P.sl = d0.seed_len; P.seedtab = d0.seed32; P.seedpair = nullptr; P.dcap = P.sl + 12; P.stride = 1; P.keff = P.kmin;
   for (uint32_t p = 0; p < seg_len; ++p) prep_thread(d0, P, p);
   for (uint32_t w = 0; w < seg_len / 16 + 2; ++w) pack_thread(P, w);
   const uint32_t ntiles = (seg_len + kTile - 1) / kTile;

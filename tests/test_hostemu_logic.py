@@ -289,3 +289,62 @@ def test_sparse_first_pass_is_exact_for_any_stride(manifest, golden_searches, st
         assert sparse_runs >= 10
     if stride == 0:
         assert lookups[0] < 0.8 * lookups[1], lookups      # fewer table lookups than the dense pass makes
+
+
+def test_range_that_starts_below_the_table_depth(manifest, golden_searches, tmp_path):
+    """k = a:b with a below the depth of the derived table (BASELINE configs[4]: 12:255 on the 16-letter table): chains
+    start from the derived table, lengths below its depth are settled with exact counts where the table does not rule
+    them out (subdepth_candidate).  Same bytes as the reference's for every golden range run that qualifies, with the
+    path on and off (bit 30 of the stride argument = NM_OPT_SUBDEPTH 1), and for random genomes against the oracle."""
+    cache, used = {}, 0
+    for run in manifest["searches"]:
+        if not run["range"]:
+            continue
+        seed = manifest["indexes"][run["index"]]["seed_length"]
+        klist = run_klist(run)
+        for depth in {min(max(klist), min(klist) + 1 + run["id"] % 2, 11), min(max(klist), min(klist) + 3, 11)}:   # (host RAM: 16 B x 4^depth)
+            if not (seed <= min(klist) < depth <= max(klist)) or depth <= seed:
+                continue
+            ix = cache.get((run["index"], depth))
+            if ix is None:
+                ix = cache[(run["index"], depth)] = EmuIndex(GOLD / f"{run['index']}.awfmi").set_seed_depth(depth)
+            for off in (0, 0x40000000):
+                got = {}
+                for seg, n in _segments(run):
+                    out, stats = ix.min_unique_segment(seg.data, n, klist, True, run.get("initial", 0),
+                                                       not run.get("norc", False), 0, stride=off)
+                    assert stats[3] == 0 and stats[4] == -1, (run["id"], stats)
+                    got.setdefault(seg.id, []).append(out)
+                for sid, parts in got.items():
+                    want = golden_searches[f"run{run['id']}|{sid.decode()}"]
+                    arr = np.concatenate(parts)
+                    bad = np.nonzero(arr != want)[0]
+                    assert bad.size == 0, (depth, off, run, sid, bad[:10], arr[bad[:10]], want[bad[:10]])
+            used += 1
+    assert used >= 8, used
+    if not ora.ref_available():
+        return
+    rng = np.random.default_rng(99)
+    for trial in range(4):
+        n = int(rng.integers(3000, 9000))
+        alphabet = np.frombuffer(b"ACGT" if trial % 2 else b"ACGTacgtN", dtype=np.uint8)
+        a = alphabet[rng.integers(0, alphabet.size, n)].copy()
+        a[n // 2:n // 2 + 300] = a[100:400]
+        fa = tmp_path / f"s{trial}.fa"
+        fa.write_bytes(b">s\n" + a.tobytes() + b"\n")
+        ixp = tmp_path / f"s{trial}.awfmi"
+        ora.ref_build_index(fa, ixp, 8, 3)
+        o = ora.OracleIndex(ixp)
+        e = EmuIndex(ixp).set_seed_depth(7 + trial % 2)         # a 6 k genome: many 5- and 6-mers are already unique
+        for klist in (list(range(3, 40)), list(range(5, 12)), list(range(4, 8 + trial % 2))):
+            for batch in (n, 977):
+                for seg in ora.segments(fa, batch, max(klist) - 1):
+                    m = len(seg.data) if seg.epilogue else len(seg.data) - (max(klist) - 1)
+                    want = o.min_unique_segment(seg.data, m, klist, True, nthreads=1)
+                    for norc in (False, True):
+                        if norc:
+                            want = o.min_unique_segment(seg.data, m, klist, True, use_rc=False, nthreads=1)
+                        got, st = e.min_unique_segment(seg.data, m, klist, True, use_rc=not norc, algo=0)
+                        bad = np.nonzero(got != want)[0]
+                        assert bad.size == 0, (trial, klist[0], klist[-1], batch, norc, bad[:10], got[bad[:10]], want[bad[:10]])
+                        assert (want[want > 0] < 7).any()           # answers below the table depth do occur here

@@ -1189,7 +1189,7 @@ NM_HD uint64_t ref_trajectory_steps(const SegParams &P, uint32_t sl, uint32_t li
   return total;
 }
 
-NM_HD void resolve_thread(const DevIndex &ix, const SegParams &P, uint32_t i, uint64_t &ref_lf, uint32_t &steps) {
+NM_HD void resolve_thread(const DevIndex &ix, const SegParams &P, uint32_t i, uint64_t &ref_lf) {
   uint32_t ans = 0;
   if (!(P.codes[i] & kNoStart)) {
     const uint32_t r = P.use_rc ? P.R[i] : 0u;
@@ -1214,19 +1214,6 @@ NM_HD void resolve_thread(const DevIndex &ix, const SegParams &P, uint32_t i, ui
         }
         if (P.want_ref_lf) ref_lf += ref_trajectory_steps(P, ix.seed_len, lim, ans, P.use_rc ? r : 0u);
       }
-      if (P.kmin < kq && lim >= P.kmin) {
-        // lengths kmin .. kq-1, below the table depth: possible only where the position is unique at kq (or cannot
-        // reach kq at all), and not ruled out by the table (subdepth_candidate) -- exact counts with the reference's
-        // own count (count_both) from the longest such length downwards
-        const bool cand = lim < kq ? true : (ans == kq && (P.sub[i] || (P.codes[i] & kSeedBad)));
-        if (cand) {
-          uint32_t k = lim < kq ? lim : kq - 1u;
-          if (count_both(ix, P.seg, i, k, P.use_rc != 0, steps) == 1u) {
-            while (k > P.kmin && count_both(ix, P.seg, i, k - 1u, P.use_rc != 0, steps) == 1u) --k;
-            ans = k;
-          }
-        }
-      }
     } else {
       const uint32_t b = next_barrier(P, i);
       for (uint32_t j = 0; j < P.nk; ++j) {
@@ -1238,6 +1225,66 @@ NM_HD void resolve_thread(const DevIndex &ix, const SegParams &P, uint32_t i, ui
     }
   }
   store_out(P, i, ans);
+}
+
+// (S) lengths kmin .. keff-1, below the depth of the table the chains started from (range mode, keff > kmin): after
+// resolve_thread.  Possible only where the position is unique at keff -- or cannot reach keff at all -- and where the
+// table does not rule it out (P.sub, subdepth_candidate): exact two-strand counts from the longest such length
+// downwards (the count is non-increasing in the length).  A clean window is counted on the rank32 layout from the
+// file's own seed table (its last seed_len letters looked up, the rest one step each); anything else -- an
+// irregular letter nearby, a barrier or the segment end before keff -- with the reference's own count (count_both).
+NM_HD uint32_t count_clean_fast(const DevIndex &ix, const uint32_t *C32, const SegParams &P, uint32_t i, uint32_t k,
+                                uint32_t &steps) {
+  // S[i, i+k), k >= seed_len, inside a clean window of P.sl >= k letters starting at i: 2-bit letters from pk
+  const uint32_t fsl = ix.seed_len;
+  const uint32_t w = window_key(P, i);                       // P.sl letters, the first one most significant
+  auto letter_at = [&](uint32_t j) -> unsigned { return (w >> (2u * (P.sl - 1u - j))) & 3u; };   // letter i + j
+  uint32_t total = 0;
+  {  // forward strand: the last fsl letters from the table, then leftwards
+    uint32_t key = 0;
+    for (uint32_t j = k - fsl; j < k; ++j) key = (key << 2) | letter_at(j);
+    const SeedEntry32 e = ix.seed32[key];
+    uint32_t lo = e.start, hi = e.start + e.len;
+    for (uint32_t j = k - fsl; j-- > 0u && lo < hi;) { lf_fast(ix, C32, letter_at(j), lo, hi); ++steps; }
+    total += hi > lo ? hi - lo : 0u;
+  }
+  if (P.use_rc) {  // other strand: the pattern is comp(S[i+k-1]) .. comp(S[i]); its last fsl letters are comp of S[i+fsl-1] .. S[i]
+    uint32_t key = 0;
+    for (uint32_t j = fsl; j-- > 0u;) key = (key << 2) | (3u - letter_at(j));
+    const SeedEntry32 e = ix.seed32[key];
+    uint32_t lo = e.start, hi = e.start + e.len;
+    for (uint32_t j = fsl; j < k && lo < hi; ++j) { lf_fast(ix, C32, 3u - letter_at(j), lo, hi); ++steps; }
+    total += hi > lo ? hi - lo : 0u;
+  }
+  return total;
+}
+
+NM_HD void subdepth_thread(const DevIndex &ix, const uint32_t *C32, const SegParams &P, uint32_t i, uint32_t &steps) {
+  const uint8_t c = P.codes[i];
+  if (c & kNoStart) return;
+  const uint32_t kq = P.keff;
+  const bool clean = !(c & kSeedBad);                      // then no barrier within P.sl = kq letters either: lim >= kq
+  uint32_t ans;
+  uint32_t lim = kq;
+  if (clean) {
+    if (!P.sub[i]) return;
+    ans = load_out(P, i);
+    if (ans != kq) return;                                 // not unique at kq: not unique at anything shorter
+  } else {
+    lim = length_limit(P, i);
+    if (lim < P.kmin) return;
+    ans = load_out(P, i);
+    if (lim >= kq && ans != kq) return;
+  }
+  uint32_t k = lim < kq ? lim : kq - 1u;
+  if (clean) {
+    if (count_clean_fast(ix, C32, P, i, k, steps) != 1u) return;
+    while (k > P.kmin && count_clean_fast(ix, C32, P, i, k - 1u, steps) == 1u) --k;
+  } else {
+    if (count_both(ix, P.seg, i, k, P.use_rc != 0, steps) != 1u) return;
+    while (k > P.kmin && count_both(ix, P.seg, i, k - 1u, P.use_rc != 0, steps) == 1u) --k;
+  }
+  store_out(P, i, k);
 }
 
 // ---------------------------------------------------------------------------------------------

@@ -478,10 +478,18 @@ __global__ void __launch_bounds__(kBlock) k_free_generic(DevIndex ix, SegParams 
 __global__ void __launch_bounds__(kBlock) k_resolve(DevIndex ix, SegParams P) {
   const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
   uint64_t ref_lf = 0;
-  uint32_t steps = 0;
-  if (i < P.num_kmers) resolve_thread(ix, P, i, ref_lf, steps);
+  if (i < P.num_kmers) resolve_thread(ix, P, i, ref_lf);
   if (P.want_ref_lf) flush_counter64(&P.counters[CTR_REF_LF], ref_lf);
-  if (P.keff > P.kmin) flush_counter(&P.counters[CTR_LF], steps);
+}
+
+// lengths below the depth of the table the chains started from (subdepth_thread, nm_core.cuh): after k_resolve
+__global__ void __launch_bounds__(kBlock) k_subdepth(DevIndex ix, SegParams P) {
+  __shared__ uint32_t sC[8];
+  const uint32_t *C32 = stage_c32(ix, sC);
+  const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+  uint32_t steps = 0;
+  if (i < P.num_kmers) subdepth_thread(ix, C32, P, i, steps);
+  flush_counter(&P.counters[CTR_LF], steps);
 }
 
 // NM_OPT_OUT_STATS: what `newmap search --verbose` reports per sequence (search.py:318-347,885-902), reduced on the device
@@ -612,6 +620,10 @@ void launch_free_generic(const DevIndex &ix, const SegParams &P, bool all, cudaS
 void launch_resolve(const DevIndex &ix, const SegParams &P, cudaStream_t st) {
   if (P.num_kmers == 0) return;
   k_resolve<<<grid_for(P.num_kmers), kBlock, 0, st>>>(ix, P);
+}
+void launch_subdepth(const DevIndex &ix, const SegParams &P, cudaStream_t st) {
+  if (P.num_kmers == 0) return;
+  k_subdepth<<<grid_for(P.num_kmers), kBlock, 0, st>>>(ix, P);
 }
 void launch_out_stats(const SegParams &P, cudaStream_t st) {
   if (P.num_kmers == 0) return;

@@ -23,6 +23,7 @@ void launch_coarse_anchor(const DevIndex &ix, const SegParams &P, CoarseGroup *g
 void launch_coarse_settle(const SegParams &P, const CoarseGroup *groups, cudaStream_t st);
 void launch_free_generic(const DevIndex &ix, const SegParams &P, bool all, cudaStream_t st);
 void launch_resolve(const DevIndex &ix, const SegParams &P, cudaStream_t st);
+void launch_subdepth(const DevIndex &ix, const SegParams &P, cudaStream_t st);
 void launch_out_stats(const SegParams &P, cudaStream_t st);
 void launch_checksum(const void *out, int out_width, uint64_t n, unsigned long long *sum, cudaStream_t st);
 void launch_probe(const uint8_t *buf, uint64_t n_granules_pow2, uint32_t granule, uint64_t chains, uint32_t steps,

@@ -366,6 +366,10 @@ int run_search(nm_workspace *ws, int algo) {
     NM_CUDA(cudaEventRecord(ws->ev[EV_GENERIC1], st));
     nm::launch_resolve(ix->dev, P, st);
     ws->launches += P.num_kmers ? 1u : 0u;
+    if (P.keff > P.kmin) {   // a range that starts below the depth of the table in use: the lengths below it
+      nm::launch_subdepth(ix->dev, P, st);
+      ws->launches += P.num_kmers ? 1u : 0u;
+    }
     NM_CUDA(cudaEventRecord(ws->ev[EV_RESOLVE1], st));
   }
   if (ws->opt_out_stats) {

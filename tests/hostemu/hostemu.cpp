@@ -174,7 +174,8 @@ int emu_min_unique(EmuIndex *ix, const uint8_t *seg, uint32_t seg_len, uint32_t 
     } else {
       for (uint32_t p = 0; p <= seg_len; ++p) free_generic_thread(ix->dev, P, p, true, steps, ns);
     }
-    for (uint32_t i = 0; i < num_kmers; ++i) resolve_thread(ix->dev, P, i, ref_lf, steps);
+    for (uint32_t i = 0; i < num_kmers; ++i) resolve_thread(ix->dev, P, i, ref_lf);
+    if (P.keff > P.kmin) for (uint32_t i = 0; i < num_kmers; ++i) subdepth_thread(ix->dev, ix->c32, P, i, steps);
   }
   if (stats) {
     stats[0] = steps; stats[1] = nq; stats[2] = ns; stats[3] = (int64_t)ctr[CTR_ANOMALY];

@@ -145,7 +145,7 @@ int nm_workspace_sync(nm_workspace *ws, nm_stats *stats);
 /* Tuning / instrumentation knobs of a workspace; none of them changes a result byte. */
 #define NM_OPT_REF_LF 1   /* 1: also compute stats.ref_lf_steps (LF steps of the reference's trajectory) and, for that,
                              start the chains from the file's seed table instead of the derived one; default 0 */
-#define NM_OPT_DCAP 2     /* first-pass depth cap of the trajectory-free search, characters; 0 = seed depth in use + 8 (derived
+#define NM_OPT_DCAP 2     /* first-pass depth cap of the trajectory-free search, characters; 0 = seed depth in use + 3 (derived
                              table) or + 12 (the file's table) */
 #define NM_OPT_GSIZE 3    /* positions per certificate group; 0 = 20 */
 #define NM_OPT_PASS1 4    /* kernel of the first pass: 0 = chosen from the seed depth in use (default), 1 = one thread per
@@ -168,6 +168,13 @@ int nm_workspace_sync(nm_workspace *ws, nm_stats *stats);
                              table): 0 (default) = chains start from the derived table and the lengths below its depth are
                              settled with exact counts for the few positions the table does not rule out; 1 = the whole
                              search falls back to the file's own table */
+#define NM_OPT_STRICT 12  /* strict index / sequence check for NM_ALGO_AUTO.  The reference raises on the first queried k-mer
+                             whose count is 0 (search.py:699-722); the trajectory-free passes see an absent string only when
+                             a chain of theirs runs into it, which a difference inside a near-identical repeat can escape.
+                             > 0: one more backward search per block of `value` start positions (1 = 1024) proves every k-mer
+                             the reference could query present; on failure the segment is replayed on the reference's own
+                             trajectory, so bytes and error are the reference's in every case.  Costs about
+                             (value + max_k) / value LF steps per position.  Default 0 (off) */
 int nm_workspace_option(nm_workspace *ws, int option, uint64_t value);
 /* 64-bit FNV-style checksum of the last search's output computed on the device (for
  * device-resident runs that never copy the output back). */

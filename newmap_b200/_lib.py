@@ -11,7 +11,8 @@ from pathlib import Path
 import numpy as np
 
 PKG_DIR = Path(__file__).resolve().parent
-LIB_PATH = PKG_DIR / "libnewmap_b200.so"
+# (NEWMAP_B200_LIB: another build of the same library, for tuning experiments)
+LIB_PATH = Path(os.environ.get("NEWMAP_B200_LIB") or PKG_DIR / "libnewmap_b200.so")
 
 NM_MODE_RANGE, NM_MODE_LIST = 0, 1
 NM_ALGO_AUTO, NM_ALGO_TRAJECTORY, NM_ALGO_FREE_GENERIC = 0, 1, 2
@@ -290,10 +291,10 @@ class Workspace:
             pass
 
     def option(self, name: str, value: int):
-        """'ref_lf' | 'dcap' | 'gsize' | 'pass1' | 'gsize2' | 'own_chains' | 'stall' | 'cert_runs' | 'stride' | 'out_stats' | 'subdepth'
+        """'ref_lf' | 'dcap' | 'gsize' | 'pass1' | 'gsize2' | 'own_chains' | 'stall' | 'cert_runs' | 'stride' | 'out_stats' | 'subdepth' | 'strict'
         (NM_OPT_*): instrumentation / tuning, never changes results."""
         check(load().nm_workspace_option(self._h, {"ref_lf": 1, "dcap": 2, "gsize": 3, "pass1": 4, "gsize2": 5, "own_chains": 6,
-                                                   "stall": 7, "cert_runs": 8, "stride": 9, "out_stats": 10, "subdepth": 11}[name], int(value)),
+                                                   "stall": 7, "cert_runs": 8, "stride": 9, "out_stats": 10, "subdepth": 11, "strict": 12}[name], int(value)),
               "nm_workspace_option")
 
     def attach(self, fasta: "Fasta", seq_offset: int, seg_len: int):

@@ -223,6 +223,9 @@ NM_HD void lf_native(const DevIndex &ix, Range64 &r, unsigned letter) {
 // ---------------------------------------------------------------------------------------------
 // rank on the derived 32-byte layout (a,c,g,t only; bwt_len < 2^32-1)
 // block = { u32 count[4] | u64 plane0 | u64 plane1 }, code = plane1<<1 | plane0, 64 positions.
+// count[l] = prefixSums[l] + occurrences of l before the block: the rank of a position inside the block IS the new
+// suffix-array pointer of the backward-extension step (AwFmSearch.c:44-95 adds the prefix sum after the rank; here it
+// is folded in when the layout is derived, one add and one table lookup less on every dependent step).
 // A block that holds an x or $ symbol carries kPoison in all four counts.  One block = one 32-byte
 // DRAM sector, fetched with a single 256-bit load (LDG.E.256 on sm_100a).
 // ---------------------------------------------------------------------------------------------
@@ -249,14 +252,30 @@ NM_HD Rank32Block ld_rank32(const uint32_t *rank32, uint32_t blk) {
   return r;
 }
 
+#if defined(NM_BRANCHY_SEL)   // (round-1 form, kept for A/B runs: tools/sweep_opts.py with NEWMAP_B200_LIB)
 NM_HD uint32_t sel4(unsigned letter, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
   return letter == 0 ? a : letter == 1 ? b : letter == 2 ? c : d;
 }
-
 NM_HD uint32_t occ_in_block(const Rank32Block &b, unsigned letter, uint32_t off) {
   const uint64_t m = ((letter & 1u) ? b.p0 : ~b.p0) & ((letter & 2u) ? b.p1 : ~b.p1);
   return sel4(letter, b.c[0], b.c[1], b.c[2], b.c[3]) + (uint32_t)popc64(m & ((1ull << off) - 1ull));
 }
+#else
+NM_HD uint32_t sel4(unsigned letter, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  // branch-free (the lanes of a warp hold different letters: a branch per letter would run four paths one after the other)
+  const uint32_t m1 = 0u - (letter & 1u), m2 = 0u - ((letter >> 1) & 1u);
+  const uint32_t lo = a ^ ((a ^ b) & m1), hi = c ^ ((c ^ d) & m1);
+  return lo ^ ((lo ^ hi) & m2);
+}
+
+NM_HD uint32_t occ_in_block(const Rank32Block &b, unsigned letter, uint32_t off) {
+  // positions whose 2-bit code equals `letter`: plane0 must equal bit 0 of the letter, plane1 bit 1 (x ^ ~M = x where the
+  // bit is set, ~x where it is not)
+  const uint64_t n1 = (uint64_t)(letter & 1u) - 1ull, n2 = (uint64_t)((letter >> 1) & 1u) - 1ull;   // ~M1, ~M2
+  const uint64_t m = (b.p0 ^ n1) & (b.p1 ^ n2);
+  return sel4(letter, b.c[0], b.c[1], b.c[2], b.c[3]) + (uint32_t)popc64(m & ((1ull << off) - 1ull));
+}
+#endif
 
 // one backward-extension step of the half-open interval [lo,hi) by `letter` (0..4) with u32 pointers:
 // rank32 blocks for a,c,g,t (one sector when both bounds share a block), the unmodified .awfmi block
@@ -272,10 +291,9 @@ NM_HD void lf_fast(const DevIndex &ix, const uint32_t *C32, unsigned letter, uin
     const uint32_t nlo = occ_in_block(a, letter, lo & 63u);
     const uint32_t nhi = occ_in_block(b, letter, hi & 63u);
     const bool poison = a.c[0] == kPoison || b.c[0] == kPoison;
-    if (!poison) {
-      const uint32_t c = C32[letter];
-      lo = c + nlo;
-      hi = c + nhi;
+    if (!poison) {      // (the block counts include the prefix sum of the letter)
+      lo = nlo;
+      hi = nhi;
       return;
     }
   }
@@ -1227,6 +1245,44 @@ NM_HD void resolve_thread(const DevIndex &ix, const SegParams &P, uint32_t i, ui
   store_out(P, i, ans);
 }
 
+// (V) strict mode (NM_OPT_STRICT): is every k-mer the reference could query present in the index?
+// The reference raises on the first queried k-mer whose two-strand count is 0 (search.py:699-722) -- possible only
+// when the sequence does not match the index.  The trajectory-free passes notice an absent string only when one of
+// their chains runs into it, and a chain stops as soon as its interval has size 1, so a difference inside a
+// near-identical repeat can go unseen.  Every queried k-mer is a prefix of S[i, i + lim(i)); all of those for the
+// starts of a block [t*B, (t+1)*B) lie inside S[t*B, (t+1)*B - 1 + kmax), cut at barriers (no queried k-mer contains
+// one): ONE backward search per barrier-free stretch of that string proves them all present, at (B + kmax) / B
+// steps per position.  An empty interval raises CTR_ANOMALY, upon which nm_workspace_sync replays the segment on the
+// reference's own trajectory, which reports the reference's error -- or none, when the reference's trajectory never
+// queries the absent string; either way the bytes and the exception are the reference's.
+NM_HD void presence_thread(const DevIndex &ix, const uint32_t *C32, const SegParams &P, uint32_t t, uint32_t B, uint32_t &steps) {
+  const uint64_t first = (uint64_t)t * B;
+  if (first >= P.num_kmers) return;
+  uint64_t last_start = first + B - 1u;
+  if (last_start >= P.num_kmers) last_start = P.num_kmers - 1u;
+  uint64_t end = last_start + P.kmax;                       // one past the last letter any window of the block reaches
+  if (end > P.seg_len) end = P.seg_len;
+  bool have = false;
+  uint32_t lo = 0, hi = 0;
+  for (uint64_t p = end; p-- > first;) {
+    const uint8_t c = P.codes[p];
+    if (c & kBarrier) { have = false; continue; }
+    const unsigned letter = c & kLetterMask;
+    if (!have) {
+      lo = C32[letter];
+      hi = C32[letter + 1u];
+      have = true;
+    } else {
+      lf_fast(ix, C32, letter, lo, hi);
+      ++steps;
+    }
+    if (lo >= hi) {
+      atomic_or64(&P.counters[CTR_ANOMALY], 1ull);
+      return;
+    }
+  }
+}
+
 // (S) lengths kmin .. keff-1, below the depth of the table the chains started from (range mode, keff > kmin): after
 // resolve_thread.  Possible only where the position is unique at keff -- or cannot reach keff at all -- and where the
 // table does not rule it out (P.sub, subdepth_candidate): exact two-strand counts from the longest such length
@@ -1292,13 +1348,14 @@ NM_HD void subdepth_thread(const DevIndex &ix, const uint32_t *C32, const SegPar
 // one thread per 64 BWT positions (a quarter of a native block)
 // ---------------------------------------------------------------------------------------------
 NM_HD void transcode_thread(const uint8_t *native, uint64_t n_blocks, uint64_t bwt_len, uint32_t *rank32,
-                            uint64_t b64) {
+                            uint64_t b64, uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3) {
+  const uint32_t C[4] = {c0, c1, c2, c3};   // prefixSums of a, c, g, t: folded into the block counts
   const uint64_t nb = b64 >> 2;
   const unsigned w = (unsigned)(b64 & 3);
   uint32_t *o = rank32 + b64 * kRank32Words;
   if (nb >= n_blocks) {  // pad block(s): only ever read with an empty mask
     const uint64_t *last = reinterpret_cast<const uint64_t *>(native + n_blocks * kNativeBlockBytes);  // pad block counters = totals
-    for (int l = 0; l < 4; ++l) o[l] = (uint32_t)last[12 + l];
+    for (int l = 0; l < 4; ++l) o[l] = C[l] + (uint32_t)last[12 + l];
     o[4] = o[5] = o[6] = o[7] = 0;
     return;
   }
@@ -1321,7 +1378,7 @@ NM_HD void transcode_thread(const uint8_t *native, uint64_t n_blocks, uint64_t b
   if (other) {
     o[0] = o[1] = o[2] = o[3] = kPoison;
   } else {
-    for (int l = 0; l < 4; ++l) o[l] = (uint32_t)cnt[l];
+    for (int l = 0; l < 4; ++l) o[l] = C[l] + (uint32_t)cnt[l];
   }
   o[4] = (uint32_t)plane0;
   o[5] = (uint32_t)(plane0 >> 32);
@@ -1359,10 +1416,10 @@ NM_HD void seed_extend_thread(const DevIndex &ix, const uint32_t *C32, const See
       nlo = occ_in_block(a, c, lo & 63u);
       nhi = occ_in_block(b, c, hi & 63u);
     } else {
-      nlo = (uint32_t)occ_native(ix.native, c, lo);
-      nhi = (uint32_t)occ_native(ix.native, c, hi);
+      nlo = C32[c] + (uint32_t)occ_native(ix.native, c, lo);
+      nhi = C32[c] + (uint32_t)occ_native(ix.native, c, hi);
     }
-    dst[c * stride + key] = SeedEntry32{nhi > nlo ? C32[c] + nlo : 0u, nhi > nlo ? nhi - nlo : 0u};
+    dst[c * stride + key] = SeedEntry32{nhi > nlo ? nlo : 0u, nhi > nlo ? nhi - nlo : 0u};
   }
 }
 

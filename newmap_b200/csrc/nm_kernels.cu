@@ -11,6 +11,16 @@ namespace nm {
 namespace {
 
 constexpr int kBlock = 256;
+// resident blocks per SM the register allocation aims at (tuning experiments build variants with other values)
+#ifndef NM_CHAIN_MINB
+#define NM_CHAIN_MINB 8
+#endif
+#ifndef NM_P1_MINB
+#define NM_P1_MINB 6
+#endif
+#ifndef NM_CERT_MINB
+#define NM_CERT_MINB 16
+#endif
 
 inline unsigned grid_for(uint64_t n, int block = kBlock) { return (unsigned)((n + block - 1) / block); }
 
@@ -25,9 +35,9 @@ __device__ __forceinline__ void flush_counter64(unsigned long long *ctr, unsigne
 }
 
 __global__ void __launch_bounds__(kBlock) k_transcode(const uint8_t *native, uint64_t n_blocks, uint64_t bwt_len,
-                                                      uint32_t *rank32, uint64_t n64_total) {
+                                                      uint32_t *rank32, uint64_t n64_total, uint4 C) {
   const uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (t < n64_total) transcode_thread(native, n_blocks, bwt_len, rank32, t);
+  if (t < n64_total) transcode_thread(native, n_blocks, bwt_len, rank32, t, C.x, C.y, C.z, C.w);
 }
 
 __global__ void __launch_bounds__(kBlock) k_seed_transcode(const uint64_t *seed64, SeedEntry32 *seed32, uint64_t n) {
@@ -182,7 +192,7 @@ __device__ __forceinline__ const uint32_t *stage_c32(const DevIndex &ix, uint32_
 }
 
 // pass 1 (first = true): every position, depth-capped; pass 3 (first = false): positions still kDeep
-__global__ void __launch_bounds__(kBlock, 8) k_free_chain(DevIndex ix, SegParams P, bool first) {
+__global__ void __launch_bounds__(kBlock, NM_CHAIN_MINB) k_free_chain(DevIndex ix, SegParams P, bool first) {
   __shared__ uint32_t sC[8];
   const uint32_t *C32 = stage_c32(ix, sC);
   // (giving the two chains of a position to different warps in pass 3 was measured slower: 0.134 against 0.110 ms)
@@ -209,7 +219,7 @@ __global__ void __launch_bounds__(kBlock, 8) k_free_chain(DevIndex ix, SegParams
 constexpr int kSpCells = 2;                              // cells per thread
 constexpr int kSpItems = 2 * kSpCells * kBlock + 8;      // sides a block can queue (+ the head cell of block 0)
 
-__global__ void __launch_bounds__(kBlock, 6) k_pass1_sparse(DevIndex ix, SegParams P) {
+__global__ void __launch_bounds__(kBlock, NM_P1_MINB) k_pass1_sparse(DevIndex ix, SegParams P) {
   __shared__ uint32_t sC[8];
   __shared__ uint4 s_items[kSpItems];    // {position, lo, hi, depth | kind << 31 | needs-seed << 30}
   __shared__ uint32_t s_limit[kSpItems]; // last end of the cell (forward side) / first start of the cell (other strand)
@@ -409,12 +419,11 @@ __global__ void __launch_bounds__(kBlock, 6) k_pass1_sparse(DevIndex ix, SegPara
     } else if (action == 1u) {
       uint32_t nlo = occ_in_block(A, letter, s.lo & 63u), nhi = occ_in_block(B, letter, s.hi & 63u);
       if (A.c[0] == kPoison || B.c[0] == kPoison) {      // a block with an x or $ symbol: the unmodified .awfmi block
-        nlo = (uint32_t)occ_native(ix.native, letter, s.lo);
-        nhi = (uint32_t)occ_native(ix.native, letter, s.hi);
+        nlo = C32[letter] + (uint32_t)occ_native(ix.native, letter, s.lo);
+        nhi = C32[letter] + (uint32_t)occ_native(ix.native, letter, s.hi);
       }
-      const uint32_t c = C32[letter];
-      s.lo = c + nlo;
-      s.hi = c + nhi;
+      s.lo = nlo;   // (the block counts include the prefix sum of the letter)
+      s.hi = nhi;
       ++s.d;
       ++steps;
       stalled = chain_stalled(P, stall, s);
@@ -435,7 +444,7 @@ __global__ void __launch_bounds__(kBlock, 6) k_pass1_sparse(DevIndex ix, SegPara
 }
 
 // pass 2: two threads per group of P.gsize positions (forward-strand chain, other-strand chain)
-__global__ void __launch_bounds__(64, 16) k_free_cert(DevIndex ix, SegParams P, uint32_t ngroups) {
+__global__ void __launch_bounds__(64, NM_CERT_MINB) k_free_cert(DevIndex ix, SegParams P, uint32_t ngroups) {
   __shared__ uint32_t sC[8];
   const uint32_t *C32 = stage_c32(ix, sC);
   // a warp = 32 consecutive groups of ONE strand (even warps: forward, odd warps: other strand): the two halves of
@@ -480,6 +489,16 @@ __global__ void __launch_bounds__(kBlock) k_resolve(DevIndex ix, SegParams P) {
   uint64_t ref_lf = 0;
   if (i < P.num_kmers) resolve_thread(ix, P, i, ref_lf);
   if (P.want_ref_lf) flush_counter64(&P.counters[CTR_REF_LF], ref_lf);
+}
+
+// strict mode (presence_thread, nm_core.cuh): one long chain per block of B start positions, beside the search
+__global__ void __launch_bounds__(64) k_presence(DevIndex ix, SegParams P, uint32_t B, uint32_t nblocks) {
+  __shared__ uint32_t sC[8];
+  const uint32_t *C32 = stage_c32(ix, sC);
+  const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+  uint32_t steps = 0;
+  if (t < nblocks) presence_thread(ix, C32, P, t, B, steps);
+  flush_counter(&P.counters[CTR_LF], steps);
 }
 
 // lengths below the depth of the table the chains started from (subdepth_thread, nm_core.cuh): after k_resolve
@@ -564,8 +583,9 @@ __global__ void __launch_bounds__(kBlock) k_probe(const uint32_t *buf, uint32_t 
 }  // namespace
 
 void launch_transcode(const uint8_t *native, uint64_t n_blocks, uint64_t bwt_len, uint32_t *rank32,
-                      uint64_t n64_total, cudaStream_t st) {
-  k_transcode<<<grid_for(n64_total), kBlock, 0, st>>>(native, n_blocks, bwt_len, rank32, n64_total);
+                      uint64_t n64_total, const uint64_t *prefix_sums, cudaStream_t st) {
+  const uint4 C = make_uint4((uint32_t)prefix_sums[0], (uint32_t)prefix_sums[1], (uint32_t)prefix_sums[2], (uint32_t)prefix_sums[3]);
+  k_transcode<<<grid_for(n64_total), kBlock, 0, st>>>(native, n_blocks, bwt_len, rank32, n64_total, C);
 }
 void launch_seed_transcode(const uint64_t *seed64, SeedEntry32 *seed32, uint64_t entries, cudaStream_t st) {
   k_seed_transcode<<<grid_for(entries), kBlock, 0, st>>>(seed64, seed32, entries);
@@ -620,6 +640,11 @@ void launch_free_generic(const DevIndex &ix, const SegParams &P, bool all, cudaS
 void launch_resolve(const DevIndex &ix, const SegParams &P, cudaStream_t st) {
   if (P.num_kmers == 0) return;
   k_resolve<<<grid_for(P.num_kmers), kBlock, 0, st>>>(ix, P);
+}
+void launch_presence(const DevIndex &ix, const SegParams &P, uint32_t B, cudaStream_t st) {
+  if (P.num_kmers == 0) return;
+  const uint32_t nblocks = (uint32_t)(((uint64_t)P.num_kmers + B - 1) / B);
+  k_presence<<<grid_for(nblocks, 64), 64, 0, st>>>(ix, P, B, nblocks);
 }
 void launch_subdepth(const DevIndex &ix, const SegParams &P, cudaStream_t st) {
   if (P.num_kmers == 0) return;

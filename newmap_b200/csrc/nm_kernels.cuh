@@ -7,7 +7,7 @@
 namespace nm {
 
 void launch_transcode(const uint8_t *native, uint64_t n_blocks, uint64_t bwt_len, uint32_t *rank32,
-                      uint64_t n64_total, cudaStream_t st);
+                      uint64_t n64_total, const uint64_t *prefix_sums, cudaStream_t st);
 void launch_seed_transcode(const uint64_t *seed64, SeedEntry32 *seed32, uint64_t entries, cudaStream_t st);
 void launch_seed_extend(const DevIndex &ix, const SeedEntry32 *src, uint32_t d, SeedEntry32 *dst, cudaStream_t st);
 void launch_seed_pair(const SeedEntry32 *t, uint32_t d, SeedEntryPair *pair, cudaStream_t st);
@@ -23,6 +23,7 @@ void launch_coarse_anchor(const DevIndex &ix, const SegParams &P, CoarseGroup *g
 void launch_coarse_settle(const SegParams &P, const CoarseGroup *groups, cudaStream_t st);
 void launch_free_generic(const DevIndex &ix, const SegParams &P, bool all, cudaStream_t st);
 void launch_resolve(const DevIndex &ix, const SegParams &P, cudaStream_t st);
+void launch_presence(const DevIndex &ix, const SegParams &P, uint32_t B, cudaStream_t st);
 void launch_subdepth(const DevIndex &ix, const SegParams &P, cudaStream_t st);
 void launch_out_stats(const SegParams &P, cudaStream_t st);
 void launch_checksum(const void *out, int out_width, uint64_t n, unsigned long long *sum, cudaStream_t st);

@@ -73,12 +73,12 @@ struct nm_workspace {
   int algo_req = 0, algo_used = 0;
   bool timed_h2d = false, timed_d2h = false;
   void *pending_out = nullptr;
-  uint32_t opt_ref_lf = 0, opt_dcap = 0, opt_gsize = 0, opt_pass1 = 0, opt_gsize2 = ~0u, opt_own_chains = ~0u, opt_stall = ~0u, opt_cert_runs = 0, opt_stride = 0, opt_out_stats = 0, opt_subdepth = 0;
+  uint32_t opt_ref_lf = 0, opt_dcap = 0, opt_gsize = 0, opt_pass1 = 0, opt_gsize2 = ~0u, opt_own_chains = ~0u, opt_stall = ~0u, opt_cert_runs = 0, opt_stride = 0, opt_out_stats = 0, opt_subdepth = 0, opt_strict = 0;
   // several sequences x several indexes (nm_workspace_multi); cleared by the next upload / attach
   nm::CoarseGroup *d_cgroups = nullptr;  // coarse certificate round: 2 per group of >= kMinGsize2 positions
   uint64_t cgroup_cap = 0;
   cudaStream_t aux_stream = nullptr;     // the coarse round's anchor chains run here, beside the first pass
-  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_strict = nullptr;
   nm::MultiSet *d_multi = nullptr;
   uint8_t *d_extra[nm::kMaxMulti]{};  // extra sequences' segments, max_seg_len + 16 bytes each, allocated on demand
   uint32_t multi_ix = 0, multi_seq = 0;
@@ -253,7 +253,7 @@ int load_index(const char *path, int device, nm_index **out) {
     if (cudaMalloc(&ix->d_rank32, n64 * nm::kRank32Words * 4) != cudaSuccess) return NM_EALLOC;
     if (cudaMalloc(&ix->d_seed32, ix->seed_entries * sizeof(nm::SeedEntry32)) != cudaSuccess) return NM_EALLOC;
     ix->device_bytes += n64 * nm::kRank32Words * 4 + ix->seed_entries * sizeof(nm::SeedEntry32);
-    nm::launch_transcode(ix->dev.native, ix->n_blocks, bwt_len, (uint32_t *)ix->d_rank32, n64, 0);
+    nm::launch_transcode(ix->dev.native, ix->n_blocks, bwt_len, (uint32_t *)ix->d_rank32, n64, prefix, 0);
     nm::launch_seed_transcode(ix->dev.seed64, (nm::SeedEntry32 *)ix->d_seed32, ix->seed_entries, 0);
     NM_CUDA(cudaGetLastError());
     NM_CUDA(cudaDeviceSynchronize());
@@ -291,6 +291,7 @@ int ws_alloc(nm_workspace *ws) {
   NM_CUDA(cudaStreamCreateWithFlags(&ws->aux_stream, cudaStreamNonBlocking));
   NM_CUDA(cudaEventCreateWithFlags(&ws->ev_fork, cudaEventDisableTiming));
   NM_CUDA(cudaEventCreateWithFlags(&ws->ev_join, cudaEventDisableTiming));
+  NM_CUDA(cudaEventCreateWithFlags(&ws->ev_strict, cudaEventDisableTiming));
   NM_CUDA(cudaMalloc((void **)&ws->d_counters, nm::CTR_N * 8));
   NM_CUDA(cudaHostAlloc((void **)&ws->h_counters, nm::CTR_N * 8, cudaHostAllocDefault));
   for (auto &e : ws->ev) NM_CUDA(cudaEventCreate(&e));
@@ -322,6 +323,16 @@ int run_search(nm_workspace *ws, int algo) {
   } else {
     const bool fast = (algo != NM_ALGO_FREE_GENERIC) && ix->has_rank32 && P.kmin >= ix->dev.seed_len;
     P.fast = fast ? 1 : 0;
+    // strict mode: the presence chains (presence_thread, nm_core.cuh) need only the codes: they run on the
+    // workspace's second stream beside the passes and are joined before the counters are read
+    const bool strict = ws->opt_strict && ix->has_rank32 && P.num_kmers;
+    if (strict) {
+      NM_CUDA(cudaEventRecord(ws->ev_fork, st));
+      NM_CUDA(cudaStreamWaitEvent(ws->aux_stream, ws->ev_fork, 0));
+      nm::launch_presence(ix->dev, P, ws->opt_strict, ws->aux_stream);
+      NM_CUDA(cudaEventRecord(ws->ev_strict, ws->aux_stream));
+      ++ws->launches;
+    }
     const bool deep_passes = fast && P.dcap < P.kmax;
     // coarse round (coarse_anchor_thread, nm_core.cuh): anchor chains of max_k + gsize2 - 1 steps at fixed positions,
     // on the workspace's second stream BESIDE the first pass, settled after both.  Off by default: it removes a third
@@ -364,6 +375,7 @@ int run_search(nm_workspace *ws, int algo) {
     NM_CUDA(cudaEventRecord(ws->ev[EV_SEARCH1], st));
     if (!fast) { nm::launch_free_generic(ix->dev, P, true, st); ++ws->launches; }
     NM_CUDA(cudaEventRecord(ws->ev[EV_GENERIC1], st));
+    if (strict) NM_CUDA(cudaStreamWaitEvent(st, ws->ev_strict, 0));
     nm::launch_resolve(ix->dev, P, st);
     ws->launches += P.num_kmers ? 1u : 0u;
     if (P.keff > P.kmin) {   // a range that starts below the depth of the table in use: the lengths below it
@@ -547,6 +559,7 @@ void nm_workspace_destroy(nm_workspace *ws) {
   if (ws->aux_stream) cudaStreamDestroy(ws->aux_stream);
   if (ws->ev_fork) cudaEventDestroy(ws->ev_fork);
   if (ws->ev_join) cudaEventDestroy(ws->ev_join);
+  if (ws->ev_strict) cudaEventDestroy(ws->ev_strict);
   for (auto *p : ws->d_extra) cudaFree(p);
   cudaFree(ws->d_counters);
   if (ws->h_counters) cudaFreeHost(ws->h_counters);
@@ -703,7 +716,9 @@ int nm_workspace_search(nm_workspace *ws, uint64_t num_kmers, int mode, const ui
       P.sub = ws->d_sub;
     }
     const uint32_t sl = P.sl;
-    P.dcap = ws->opt_dcap ? ws->opt_dcap : (deep ? sl + 8 : sl + 12);
+    // (profiles/r2_sweep_*.jsonl: with the sparse first pass a shallow cap pays -- the chains that do not end within a few
+    //  steps are inside repeats, where the certificate pass settles 20 positions with one chain)
+    P.dcap = ws->opt_dcap ? ws->opt_dcap : (deep ? sl + 3 : sl + 12);
     if (P.dcap <= sl) P.dcap = sl + 1;
     P.gsize = ws->opt_gsize ? ws->opt_gsize : 20;  // profiles/r1_gsize_sweep_final_c3_1g.jsonl
     P.own_chains = ws->opt_own_chains == ~0u ? nm::kCertOwnChains : ws->opt_own_chains;
@@ -831,6 +846,10 @@ int nm_workspace_option(nm_workspace *ws, int option, uint64_t value) {
     case NM_OPT_STALL: if (value > 64) return NM_EARG; ws->opt_stall = (uint32_t)value; return NM_OK;
     case NM_OPT_CERT_RUNS: if (value > 64) return NM_EARG; ws->opt_cert_runs = (uint32_t)value; return NM_OK;
     case NM_OPT_GSIZE2: if (value > 65536) return NM_EARG; ws->opt_gsize2 = (uint32_t)value; return NM_OK;
+    case NM_OPT_STRICT:
+      if (value > (1u << 20)) return NM_EARG;
+      ws->opt_strict = value == 1 ? 1024u : (uint32_t)value;   // 1 = the default block of 1024 start positions
+      return NM_OK;
     case NM_OPT_SUBDEPTH: ws->opt_subdepth = value ? 1u : 0u; return NM_OK;
     case NM_OPT_OUT_STATS: ws->opt_out_stats = value ? 1u : 0u; return NM_OK;
     case NM_OPT_STRIDE: if (value > nm::kMaxStride) return NM_EARG; ws->opt_stride = (uint32_t)value; return NM_OK;

@@ -48,8 +48,15 @@ def build_parser() -> ArgumentParser:
                    help="accepted for compatibility; ignored on the GPU")
     q.add_argument("--device", type=int, default=None, help="CUDA device (default: $NEWMAP_B200_DEVICE or 0)")
     q.add_argument("--algorithm", choices=["auto", "trajectory", "free_generic"], default="auto",
-                   help="auto: trajectory-free kernels (same bytes as the reference); trajectory: replay the "
-                        "reference's binary / linear search on the GPU")
+                   help="auto: trajectory-free kernels (same bytes as the reference on a FASTA that matches the index); "
+                        "trajectory: replay the reference's binary / linear search on the GPU, query for query")
+    q.add_argument("--strict", action="store_true",
+                   help="with --algorithm auto: also prove that every k-mer the reference could query occurs in the index "
+                        "(about one more LF step per position).  The reference stops with 'k-mer was not found in the "
+                        "index' when the FASTA does not match the index; without --strict the default algorithm reports "
+                        "that only when one of its own searches meets the absent k-mer, which a difference inside a "
+                        "near-identical repeat can escape; with --strict (or --algorithm trajectory) the error is the "
+                        "reference's in every case")
     t = sub.add_parser("track", help="Calculate single and multi-read mappability tracks from shortest unique "
                                      "sequence lengths (on the GPU)")
     t.set_defaults(func=track.main)

@@ -71,6 +71,7 @@ class SearchConfig:
     verbose: bool = False
     device: int | None = None            # CUDA device (default: $NEWMAP_B200_DEVICE, $LOCAL_RANK, 0)
     algorithm: str = "auto"              # "auto" | "trajectory" | "free_generic" (include/newmap_b200.h)
+    strict: bool = False                 # NM_OPT_STRICT: prove every k-mer the reference could query present in the index
     rank: int = 0                        # position sharding: this process handles the segments whose running
     world_size: int = 1                  # number (over the whole FASTA) is congruent to rank modulo world_size
     log: Callable[..., None] = field(init=False, repr=False, compare=False)
@@ -117,6 +118,7 @@ class SearchConfig:
                    num_threads=args.num_threads, kmer_batch_size=args.kmer_batch_size,
                    initial_search_length=args.initial_search_length,
                    device=getattr(args, "device", None), algorithm=getattr(args, "algorithm", "auto"),
+                   strict=bool(getattr(args, "strict", False)),
                    rank=int(os.environ.get("RANK", "0")), world_size=int(os.environ.get("WORLD_SIZE", "1")))
 
 
@@ -393,6 +395,8 @@ def write_unique_counts(config: SearchConfig):
             slot = next((s for s in slots if s.job is None), None)
             if slot is None:
                 slot = _Slot(ix, requested_sequence_length, data_type.itemsize)
+                if config.strict:
+                    slot.ws.option("strict", 1)
                 slots.append(slot)
             n = len(segment.data)
             slot.inp.array[:n] = np.frombuffer(segment.data, dtype=np.uint8)
@@ -550,6 +554,9 @@ def _write_unique_counts_device(config: SearchConfig, ix: _lib.Index, data_type,
         if config.verbose:
             for s_ in slots:
                 s_.ws.option("out_stats", 1)
+        if config.strict:
+            for s_ in slots:
+                s_.ws.option("strict", 1)
 
         def write_out(slot, fd, nbytes, offset, truncate_to):
             os.pwrite(fd, memoryview(slot.out.array)[:nbytes], offset)

@@ -53,7 +53,8 @@ EmuIndex *emu_index_open(const char *path) {
   ix->dev.seed_len = sl;
   const uint64_t n64 = (nb + 1) * 4;
   ix->rank32.resize(n64 * 8);
-  for (uint64_t t = 0; t < n64; ++t) transcode_thread(ix->native.data(), nb, bwt_len, ix->rank32.data(), t);
+  for (uint64_t t = 0; t < n64; ++t)
+    transcode_thread(ix->native.data(), nb, bwt_len, ix->rank32.data(), t, (uint32_t)prefix[0], (uint32_t)prefix[1], (uint32_t)prefix[2], (uint32_t)prefix[3]);
   ix->seed32.resize(entries);
   for (uint64_t t = 0; t < entries; ++t) seed_transcode_thread(ix->seed64.data(), ix->seed32.data(), t);
   for (int l = 0; l < 6; ++l) ix->c32[l] = (uint32_t)prefix[l];
@@ -124,7 +125,8 @@ int emu_min_unique(EmuIndex *ix, const uint8_t *seg, uint32_t seg_len, uint32_t 
   // ... or (nm_lib.cu) a range that starts below its depth but reaches it, the lengths below settled by resolve_thread
   const bool sub = ix->dev.seedx && mode == 0 && P.kmin < ix->dev.seedx_len && P.kmax >= ix->dev.seedx_len &&
                    P.kmin >= ix->dev.seed_len && algo == 0 && !(stride & 0x40000000u);
-  if (stride != 0xFFFFFFFFu) stride &= ~0x40000000u;     // bit 30 of the stride argument: NM_OPT_SUBDEPTH 1
+  const bool strict = stride != 0xFFFFFFFFu && (stride & 0x20000000u);   // bit 29 of the stride argument: NM_OPT_STRICT
+  if (stride != 0xFFFFFFFFu) stride &= ~0x60000000u;     // bit 30 of the stride argument: NM_OPT_SUBDEPTH 1
   const bool deep = ix->dev.seedx && (P.kmin >= ix->dev.seedx_len || sub);
   std::vector<uint8_t> subv(sub ? seg_len + 16 : 0);
   P.keff = sub ? ix->dev.seedx_len : P.kmin;
@@ -148,6 +150,11 @@ int emu_min_unique(EmuIndex *ix, const uint8_t *seg, uint32_t seg_len, uint32_t 
   } else {
     const bool fast = (algo != 2) && ix->has_rank32 && P.kmin >= ix->dev.seed_len;
     P.fast = fast;
+    if (strict && num_kmers) {   // nm_lib.cu run_search: presence chains, one per block of start positions
+      const uint32_t B = 64 + (gsize + dcap) % 100, nblocks = (num_kmers + B - 1) / B;
+      uint32_t ps = 0;
+      for (uint32_t t = 0; t < nblocks; ++t) presence_thread(ix->dev, ix->c32, P, t, B, ps);
+    }
     if (fast) {
       if (sub)   // k_pass1_sparse phase A: which starts the table does not rule out for the lengths below its depth
         for (uint32_t q = 0; q < seg_len; ++q) subv[q] = !(codes[q] & kSeedBad) && subdepth_candidate(P, q);

@@ -190,6 +190,72 @@ def test_mismatched_sequence_reports_the_reference_kmer(indexes):
         assert ora.zero_count_message(alien[p:p + ln].decode()) == str(e.value)
 
 
+@pytest.mark.skipif(not ora.ref_available(), reason="needs oracle/_ref (the reference's index builder)")
+def test_strict_mode_reports_what_the_default_algorithm_misses(nm, tmp_path):
+    """The zero-count contract (search.py:699-722; DESIGN.md "Zero counts"): a difference inside a near-identical
+    repeat that the trajectory-free chains never meet -- the reference raises, `--strict` (NM_OPT_STRICT) and
+    `--algorithm trajectory` raise the same message, the default algorithm alone writes files (documented)."""
+    from newmap_b200 import search as S
+    rng = np.random.default_rng(5)
+    acgt = np.frombuffer(b"ACGT", dtype=np.uint8)
+    a = acgt[rng.integers(0, 4, 5000)].copy()
+    unit = a[1000:1600].copy()
+    copy = unit.copy()
+    for y in (300, 360):
+        copy[y] = acgt[(int(np.nonzero(acgt == unit[y])[0][0]) + 1) % 4]
+    a[3000:3600] = copy
+    fa = tmp_path / "g.fa"
+    fa.write_bytes(b">s\n" + a.tobytes() + b"\n")
+    ixp = tmp_path / "g.awfmi"
+    ora.ref_build_index(fa, ixp, 8, 4)
+    searched = a.copy()
+    searched[1300] = copy[300]
+    bad = tmp_path / "searched.fa"
+    bad.write_bytes(b">s\n" + searched.tobytes() + b"\n")
+    kl = list(range(20, 201))
+    with pytest.raises(ora.ZeroCount) as err:
+        ora.OracleIndex(ixp).min_unique_segment(searched.tobytes(), searched.size, kl, True, nthreads=1)
+    with nm.Index(ixp, device=0) as ix:
+        assert ix.derived_seed_length > ix.seed_length
+        ws = nm.Workspace(ix, searched.size)
+        buf = nm.PinnedBuffer(searched.size)
+        buf.array[:] = searched
+        for strict, want_replay in ((0, 0), (1, 1), (64, 1)):
+            ws.option("strict", strict)
+            ws.upload(buf.ptr, searched.size)
+            ws.search(searched.size, kl, True, out_width=1)
+            st = ws.sync()
+            assert st.replayed == want_replay, (strict, st.replayed)
+            if want_replay:
+                p, ln = st.zero_pos, st.zero_len
+                assert ora.zero_count_message(searched[p:p + ln].tobytes().decode()) == str(err.value)
+        # a matching sequence: strict mode is silent and changes nothing
+        buf.array[:] = a
+        outs = []
+        for strict in (0, 1):
+            ws.option("strict", strict)
+            ws.upload(buf.ptr, a.size)
+            ws.search(a.size, kl, True, out_width=1)
+            out = nm.PinnedBuffer(a.size)
+            ws.download(out.ptr)
+            st = ws.sync()
+            assert st.replayed == 0 and st.zero_pos < 0
+            outs.append(out.array[:a.size].copy())
+        assert np.array_equal(outs[0], outs[1])
+        ws.close()
+    for kw, raises in ((dict(), False), (dict(strict=True), True), (dict(algorithm="trajectory"), True)):
+        out = tmp_path / f"o{len(kw)}{raises}"
+        out.mkdir()
+        cfg = S.SearchConfig(fasta_filepaths=[bad], fmindex_filepaths=[ixp], kmer_lengths=kl, is_binary_search=True,
+                             output_directory=out, **kw)
+        if raises:
+            with pytest.raises(RuntimeError, match="was not found in the index") as got:
+                S.write_unique_counts(cfg)
+            assert str(got.value) == str(err.value)
+        else:
+            S.write_unique_counts(cfg)
+
+
 def test_invalid_arguments(indexes):
     ix = indexes("genome_s1")
     with pytest.raises(ValueError):

@@ -348,3 +348,44 @@ def test_range_that_starts_below_the_table_depth(manifest, golden_searches, tmp_
                         bad = np.nonzero(got != want)[0]
                         assert bad.size == 0, (trial, klist[0], klist[-1], batch, norc, bad[:10], got[bad[:10]], want[bad[:10]])
                         assert (want[want > 0] < 7).any()           # answers below the table depth do occur here
+
+
+def test_strict_mode_sees_the_mismatch_the_default_algorithm_misses(tmp_path):
+    """The zero-count contract (search.py:699-722).  Two copies of a repeat differ at two sites 60 apart; the FASTA
+    that is searched carries, in one copy, the other copy's letter at the first site.  Every k-mer that spans both
+    sites is absent from the index: the reference raises.  The chains of the trajectory-free passes stop at the first
+    site they meet (one copy left = unique), so the default algorithm sees nothing; NM_OPT_STRICT does, and the replay
+    on the reference's trajectory then reports the reference's own k-mer.  On a matching FASTA strict mode is silent."""
+    if not ora.ref_available():
+        pytest.skip("needs oracle/_ref to build a fresh index")
+    rng = np.random.default_rng(5)
+    acgt = np.frombuffer(b"ACGT", dtype=np.uint8)
+    a = acgt[rng.integers(0, 4, 5000)].copy()
+    unit = a[1000:1600].copy()
+    copy = unit.copy()
+    y1, y2 = 300, 360
+    for y in (y1, y2):
+        copy[y] = acgt[(int(np.nonzero(acgt == unit[y])[0][0]) + 1) % 4]
+    a[3000:3600] = copy
+    fa = tmp_path / "g.fa"
+    fa.write_bytes(b">s\n" + a.tobytes() + b"\n")
+    ixp = tmp_path / "g.awfmi"
+    ora.ref_build_index(fa, ixp, 8, 4)
+    searched = a.copy()
+    searched[1000 + y1] = copy[y1]                      # first copy now reads like the second one at y1, not at y2
+    kl = list(range(20, 201))
+    o, e = ora.OracleIndex(ixp), EmuIndex(ixp).set_seed_depth(8)
+    with pytest.raises(ora.ZeroCount) as err:
+        o.min_unique_segment(searched.tobytes(), searched.size, kl, True, nthreads=1)
+    STRICT = 0x20000000
+    _, st = e.min_unique_segment(searched.tobytes(), searched.size, kl, True, algo=0)
+    assert st[3] == 0                                    # the default algorithm does not notice
+    _, st = e.min_unique_segment(searched.tobytes(), searched.size, kl, True, algo=0, stride=STRICT)
+    assert st[3] == 1                                    # strict mode does -> nm_workspace_sync replays on the trajectory
+    _, st = e.min_unique_segment(searched.tobytes(), searched.size, kl, True, algo=1)
+    p, ln = int(st[4]), int(st[5])
+    assert ora.zero_count_message(searched[p:p + ln].tobytes().decode()) == str(err.value)
+    for dcap, gsize in ((0, 0), (9, 7), (11, 33)):       # (they also pick the block size of the presence chains here)
+        want = o.min_unique_segment(a.tobytes(), a.size, kl, True, nthreads=1)
+        got, st = e.min_unique_segment(a.tobytes(), a.size, kl, True, algo=0, stride=STRICT, dcap=dcap, gsize=gsize)
+        assert st[3] == 0 and np.array_equal(got, want)

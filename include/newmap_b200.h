@@ -227,6 +227,9 @@ void nm_fasta_close(nm_fasta *fa);
 int nm_fasta_feed(nm_fasta *fa, const void *data, uint64_t n);
 /* appends a whole plain-text file, read by `threads` reader threads (0 = 4) straight into pinned staging */
 int nm_fasta_feed_file(nm_fasta *fa, const char *path, uint32_t threads);
+/* The same for the bytes [offset, offset + length) of the file (clipped to its size): a rank of a sharded run reads only
+ * the part of the text its windows lie in (newmap_b200/search.py, partitioned ingest). */
+int nm_fasta_feed_file_range(nm_fasta *fa, const char *path, uint64_t offset, uint64_t length, uint32_t threads);
 int nm_fasta_finish(nm_fasta *fa, nm_fasta_info *info);
 int nm_fasta_records(const nm_fasta *fa, nm_fasta_record *out, uint64_t capacity);      /* fills min(records, capacity) */
 int nm_fasta_headers(const nm_fasta *fa, char *out, uint64_t capacity, uint64_t *needed); /* packed header lines */

@@ -79,6 +79,7 @@ SIGNATURES = {
     "nm_fasta_close": (None, [_vp]),
     "nm_fasta_feed": (_i, [_vp, _vp, _u64]),
     "nm_fasta_feed_file": (_i, [_vp, C.c_char_p, _u32]),
+    "nm_fasta_feed_file_range": (_i, [_vp, C.c_char_p, _u64, _u64, _u32]),
     "nm_fasta_finish": (_i, [_vp, C.POINTER(FastaInfo)]),
     "nm_fasta_records": (_i, [_vp, C.POINTER(FastaRecord), _u64]),
     "nm_fasta_headers": (_i, [_vp, _vp, _u64, C.POINTER(_u64)]),
@@ -360,8 +361,14 @@ class Fasta:
         a = as_u8(data)
         check(load().nm_fasta_feed(self._h, a.ctypes.data, a.size), "nm_fasta_feed")
 
-    def feed_file(self, path, threads: int = 0) -> None:
-        check(load().nm_fasta_feed_file(self._h, os.fsencode(str(path)), int(threads)), f"nm_fasta_feed_file({path})")
+    def feed_file(self, path, threads: int = 0, offset: int = 0, length: int | None = None) -> None:
+        """The file's text, or its bytes [offset, offset + length), read by `threads` readers into pinned staging."""
+        if offset == 0 and length is None:
+            check(load().nm_fasta_feed_file(self._h, os.fsencode(str(path)), int(threads)), f"nm_fasta_feed_file({path})")
+        else:
+            check(load().nm_fasta_feed_file_range(self._h, os.fsencode(str(path)), int(offset),
+                                                  int(length) if length is not None else 0xFFFFFFFFFFFFFFFF, int(threads)),
+                  f"nm_fasta_feed_file_range({path})")
 
     def finish(self) -> "Fasta":
         L = load()

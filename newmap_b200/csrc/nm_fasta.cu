@@ -300,6 +300,10 @@ int nm_fasta_feed(nm_fasta *fa, const void *data, uint64_t n) {
 }
 
 int nm_fasta_feed_file(nm_fasta *fa, const char *path, uint32_t threads) {
+  return nm_fasta_feed_file_range(fa, path, 0, ~0ull, threads);
+}
+
+int nm_fasta_feed_file_range(nm_fasta *fa, const char *path, uint64_t offset, uint64_t length, uint32_t threads) {
   if (!fa || fa->finished || !path) return NM_EARG;
   FA_CUDA(cudaSetDevice(fa->device));
   const int fd = open(path, O_RDONLY);
@@ -309,7 +313,9 @@ int nm_fasta_feed_file(nm_fasta *fa, const char *path, uint32_t threads) {
     close(fd);
     return NM_EOPEN;
   }
-  const uint64_t size = (uint64_t)st.st_size;
+  const uint64_t file_size = (uint64_t)st.st_size;
+  if (offset > file_size) offset = file_size;
+  const uint64_t size = length < file_size - offset ? length : file_size - offset;   // bytes [offset, offset + size)
   int rc = fa_reserve(fa, fa->raw_len + size);
   if (rc != NM_OK) {
     close(fd);
@@ -341,7 +347,7 @@ int nm_fasta_feed_file(nm_fasta *fa, const char *path, uint32_t threads) {
       if (busy[b] && cudaEventSynchronize(ev[b]) != cudaSuccess) { ok = false; break; }
       uint64_t got = 0;
       while (got < len) {
-        const ssize_t r = pread(fd, h[b] + got, len - got, (off_t)(off + got));
+        const ssize_t r = pread(fd, h[b] + got, len - got, (off_t)(offset + off + got));
         if (r <= 0) break;
         got += (uint64_t)r;
       }

@@ -45,6 +45,9 @@ READER_THREADS = int(os.environ.get("NEWMAP_B200_READERS", "0"))   # threads rea
 # "host": newmap_b200/fasta.py cuts the segments and every segment is uploaded.  Default: device (with --verbose too:
 # the per-sequence statistics of the verbose log are a reduction on the device, NM_OPT_OUT_STATS).
 INGEST = os.environ.get("NEWMAP_B200_INGEST", "auto")
+# a run sharded by its launcher (torchrun: RANK / WORLD_SIZE / MASTER_ADDR) reads, per rank, only the part of an
+# uncompressed FASTA its windows lie in; 0 = every rank reads and parses the whole text
+PARTITIONED = os.environ.get("NEWMAP_B200_PARTITIONED", "1") != "0"
 # [(phase name, seconds since the start of the run)] of the last device-ingest run of this process (bench.py reads it)
 LAST_RUN_TRACE: list = []
 
@@ -493,11 +496,168 @@ def _write_unique_counts_multi(config: SearchConfig, data_type, unique_count_suf
                              f"{config.exclude_sequence_ids}")
 
 
+def _record_id(header: bytes) -> bytes:
+    tokens = header.split()
+    return tokens[0][1:] if tokens else b""       # fasta.py:60-75
+
+
+def _plan_groups(config: SearchConfig, records, requested_sequence_length: int, lookahead_length: int) -> list:
+    """[id, [(record number, start in record, length, num_kmers, file offset, running number)], file size] per output
+    file, from [(id, record length)]: consecutive records with the same id share one file and are APPENDED to it
+    (search.py:268-357 opens a file anew only when the id changes); a window lands where the windows before it in that
+    file end.  The include / exclude filter is evaluated exactly like search.py:268-278, quirk included."""
+    groups: list = []
+    previous_id = None
+    segment_number = -1
+    for rec_no, (seq_id, rec_len) in enumerate(records):
+        if rec_len == 0:
+            continue
+        if previous_id != seq_id:
+            if config.include_sequence_ids or config.exclude_sequence_ids:
+                if (seq_id not in config.include_sequence_ids) or (seq_id in config.exclude_sequence_ids):
+                    continue
+            previous_id = seq_id
+            groups.append([seq_id, [], 0])
+        g = groups[-1]
+        for start, length, epilogue in window_plan(rec_len, requested_sequence_length, lookahead_length):
+            num_kmers = length if epilogue else length - lookahead_length
+            segment_number += 1
+            g[1].append((rec_no, start, length, num_kmers, g[2], segment_number))
+            g[2] += num_kmers
+    return groups
+
+
+def _line_start_at_or_after(fd: int, pos: int, size: int):
+    """Smallest p >= pos that is the start of a line of the file (0, the file size, or one past a newline); None when
+    there is no newline within 64 MiB (a FASTA with whole sequences on one line: not partitioned)."""
+    if pos <= 0:
+        return 0
+    if pos >= size:
+        return size
+    at = pos - 1
+    while at < min(size, pos + (64 << 20)):
+        chunk = os.pread(fd, 1 << 20, at)
+        if not chunk:
+            break
+        k = chunk.find(b"\n")
+        if k >= 0:
+            return at + k + 1
+        at += len(chunk)
+    return size if at >= size else None
+
+
+def _all_gather(obj, world_size: int):
+    """One object per rank, in rank order, over torch.distributed (the process group of the caller, else a gloo group
+    from the launcher's MASTER_ADDR / MASTER_PORT): the only exchange of a sharded run -- a few numbers per rank."""
+    import torch.distributed as dist
+    if not dist.is_initialized():
+        dist.init_process_group("gloo")
+    out = [None] * world_size
+    dist.all_gather_object(out, obj)
+    return out
+
+
+def _partition_table(fragments: list, rank: int, local_offsets: list, tail_bases: int):
+    """The global record table of a partitioned run and this rank's view of it.
+    fragments[r] = [(id or None, bases inside r's byte range)] in file order -- None: the piece goes on with the record
+    the previous rank left open; local_offsets = where this rank's pieces begin in its own sequence buffer;
+    tail_bases = bases of its last piece's record that it read beyond its range.
+    Returns (table [[id, length, pieces [rank, first base in the record, bases, local offset]]], locate)."""
+    table: list = []
+    for r, fr in enumerate(fragments):
+        for header, own in fr:
+            if header is None and table:
+                table[-1][1] += own
+                table[-1][2].append([r, table[-1][1] - own, own, None])
+            else:
+                table.append([header if header is not None else b"", own, [[r, 0, own, None]]])
+    mine = [piece for rec in table for piece in rec[2] if piece[0] == rank]
+    for piece, off in zip(mine, local_offsets):
+        piece[3] = off
+    last_piece = mine[-1] if mine else None
+
+    def locate(rec_no: int, start: int, length: int):
+        """(owner of the window, its local sequence offset or None, fits): owner = the rank whose range holds the
+        window's first base; the bases it needs beyond its range must lie in the stretch it read after it."""
+        for piece in table[rec_no][2]:
+            r, first_base, own, off = piece
+            if first_base <= start < first_base + own:
+                if r != rank:
+                    return r, None, True
+                beyond = start + length - (first_base + own)
+                fits = beyond <= 0 or (piece is last_piece and beyond <= tail_bases)
+                return r, off + (start - first_base), fits
+        return -1, None, False          # (a record without bases has no window)
+
+    return table, locate
+
+
+def _partitioned_ingest(config: SearchConfig, ix: _lib.Index, path: Path, requested_sequence_length: int,
+                        lookahead_length: int, mark):
+    """Sharded run, uncompressed FASTA: every rank reads ONLY ITS byte range of the text (+ the stretch its last window
+    reaches into), parses it on its GPU, and the ranks exchange what they found -- header lines and base counts -- so
+    that each can lay out the same global window plan and take the windows that start in its range.
+    Returns (fasta, records [(id, length)], locate(record number, start) -> (owner rank, local sequence offset)) or
+    None when the text is not fit for it (every rank then reads the whole file: _write_unique_counts_device)."""
+    rank, world = config.rank, config.world_size
+    size = path.stat().st_size
+    fd = os.open(path, os.O_RDONLY)
+    try:
+        lo = _line_start_at_or_after(fd, size * rank // world, size)
+        hi = _line_start_at_or_after(fd, size * (rank + 1) // world, size)
+        ok = lo is not None and hi is not None
+        fa = None
+        frags, tail_first, tail_all = [], 0, 0
+        if ok:
+            # enough text after the range for the longest window that can start inside it (lines of >= 8 bases)
+            tail_len = min(size - hi, requested_sequence_length + requested_sequence_length // 4 + 65536)
+            fa = _lib.Fasta(ix.device, size_hint=hi - lo + tail_len)
+            fa.feed_file(path, READER_THREADS, offset=lo, length=hi - lo + tail_len)
+            mark("text_on_device")
+            try:
+                fa.finish()
+            except RuntimeError:
+                ok = False
+            mark("parsed")
+            ok = ok and not fa.info.odd_whitespace
+        if ok:
+            # the stretch after the range, looked at on the host: how many of the parsed bases and header lines are its
+            tail = np.frombuffer(os.pread(fd, tail_len, hi), dtype=np.uint8) if tail_len else np.zeros(0, dtype=np.uint8)
+            newline = tail == 10
+            line_start = np.empty(tail.size, dtype=bool)
+            if tail.size:
+                line_start[0] = True
+                line_start[1:] = newline[:-1]
+            headers = np.nonzero(line_start & ((tail == ord(">")) | (tail == ord(";"))))[0]
+            first = int(headers[0]) if headers.size else tail.size
+            tail_first = first - int(newline[:first].sum())          # bases of the tail before its first header line
+            recs = fa.records[:len(fa.records) - headers.size]        # the records that begin (or go on) inside the range
+            for n, (header, off, length) in enumerate(recs):
+                own = length - (tail_first if n == len(recs) - 1 else 0)
+                # a headerless first piece goes on with the record the previous rank left open (rank 0: id b"")
+                frags.append((None if (not header and n == 0 and rank > 0) else _record_id(header), off, own))
+            if not recs:
+                tail_first = 0
+            tail_all = tail_first
+    finally:
+        os.close(fd)
+    everyone = _all_gather((ok, [(h, own) for h, _, own in frags]), world)
+    mark("exchanged")
+    if not all(o for o, _ in everyone):
+        if fa is not None:
+            fa.close()
+        return None
+    table, locate = _partition_table([fr for _, fr in everyone], rank, [off for _, off, _ in frags], tail_all)
+    return fa, [(rec[0], rec[1]) for rec in table], locate
+
+
 def _write_unique_counts_device(config: SearchConfig, ix: _lib.Index, data_type, unique_count_suffix: str) -> bool:
     """write_unique_counts with the FASTA parsed on the GPU: the text is streamed to the device while it is read
     (reader threads, pinned staging), records become contiguous runs of bases there, segments are the windows
     fasta.window_plan gives and are searched in place; results come back through pinned buffers and are written by a
-    small pool of writer threads.  Returns False (nothing written) when the text needs the host reader."""
+    small pool of writer threads.  A run sharded over several ranks by its launcher (RANK / WORLD_SIZE / MASTER_ADDR in
+    the environment) reads only its part of the text (_partitioned_ingest).  Returns False (nothing written) when the
+    text needs the host reader."""
     from concurrent.futures import ThreadPoolExecutor
     max_kmer_length = max(config.kmer_lengths)
     lookahead_length = max_kmer_length - 1
@@ -510,42 +670,65 @@ def _write_unique_counts_device(config: SearchConfig, ix: _lib.Index, data_type,
 
     def mark(name):
         marks.append((name, time.perf_counter() - t_start))
-    fa = _lib.Fasta(ix.device, size_hint=path.stat().st_size if path.suffix != ".gz" else 0)
-    mark("fasta_open")
+    sharded = config.world_size > 1
+    if not 0 <= config.rank < config.world_size:
+        raise ValueError("rank must be in [0, world_size)")
     itemsize = data_type.itemsize
     slots: list = []
+    fa = None
     # workspaces and pinned output buffers are allocated while the file is being read
     maker = ThreadPoolExecutor(max_workers=1)
     made = maker.submit(lambda: [_DeviceSlot(ix, requested_sequence_length, itemsize)
                                  for _ in range(DEVICE_PIPELINE_DEPTH + max(2, WRITER_THREADS - 1))])
     try:
-        if path.suffix == ".gz":
-            with optional_gzip_open(path, "rb") as fh:
-                while True:
-                    block = fh.read(64 << 20)
-                    if not block:
-                        break
-                    fa.feed(block)
+        partitioned = None
+        if (sharded and PARTITIONED and path.suffix != ".gz" and os.environ.get("MASTER_ADDR")
+                and os.environ.get("WORLD_SIZE") == str(config.world_size) and os.environ.get("RANK") == str(config.rank)):
+            partitioned = _partitioned_ingest(config, ix, path, requested_sequence_length, lookahead_length, mark)
+        if partitioned is not None:
+            fa, records, locate = partitioned
+            groups = _plan_groups(config, records, requested_sequence_length, lookahead_length)
+            placed = [[locate(rec_no, start, length) for rec_no, start, length, _, _, _ in wins] for _, wins, _ in groups]
+            fits = all(f for row in placed for _, _, f in row)
+            if not all(_all_gather(fits, config.world_size)):
+                raise RuntimeError("partitioned ingest: a window reaches beyond the text a rank read after its range "
+                                   "(lines shorter than 8 bases?); run with NEWMAP_B200_PARTITIONED=0")
+            # [id, [(local sequence offset, length, num_kmers, file offset, mine)], file size]
+            plan = [[sid, [(off, length, nk, foff, owner == config.rank)
+                           for (_, _, length, nk, foff, _), (owner, off, _) in zip(wins, row)], total]
+                    for (sid, wins, total), row in zip(groups, placed)]
+            mark("planned")
         else:
-            fa.feed_file(path, READER_THREADS)
-        mark("text_on_device")
-        try:
-            fa.finish()
-            mark("parsed")
-        except RuntimeError:
-            return False            # e.g. more header lines than the device parser handles
-        if fa.info.odd_whitespace:
-            return False            # right-stripping beyond newlines: the host reader implements it
+            fa = _lib.Fasta(ix.device, size_hint=path.stat().st_size if path.suffix != ".gz" else 0)
+            mark("fasta_open")
+            if path.suffix == ".gz":
+                with optional_gzip_open(path, "rb") as fh:
+                    while True:
+                        block = fh.read(64 << 20)
+                        if not block:
+                            break
+                        fa.feed(block)
+            else:
+                fa.feed_file(path, READER_THREADS)
+            mark("text_on_device")
+            try:
+                fa.finish()
+                mark("parsed")
+            except RuntimeError:
+                return False            # e.g. more header lines than the device parser handles
+            if fa.info.odd_whitespace:
+                return False            # right-stripping beyond newlines: the host reader implements it
+            offsets = [off for _, off, _ in fa.records]
+            groups = _plan_groups(config, [(_record_id(h), n) for h, _, n in fa.records], requested_sequence_length,
+                                  lookahead_length)
+            plan = [[sid, [(offsets[rec_no] + start, length, nk, foff, number % config.world_size == config.rank)
+                           for rec_no, start, length, nk, foff, number in wins], total] for sid, wins, total in groups]
         slots = made.result()
         mark("slots_ready")
-        sharded = config.world_size > 1
-        if not 0 <= config.rank < config.world_size:
-            raise ValueError("rank must be in [0, world_size)")
         inflight: deque = deque()
         files: list = []
         current_sequence_id = None
         current_fd = -1
-        segment_number = -1
         # --verbose: the log lines come in the reference's order (a segment is finished before the next one is
         # announced) and the statistics of search.py:318-347 come from a reduction on the device
         depth = 1 if config.verbose else DEVICE_PIPELINE_DEPTH
@@ -582,33 +765,12 @@ def _write_unique_counts_device(config: SearchConfig, ix: _lib.Index, data_type,
                                        (offset + num_kmers) * itemsize if last_of_file else None)
             slot.job = None
 
-        # the plan: consecutive records with the same id share one file and are APPENDED to it (search.py:268-357 opens
-        # a file anew only when the id changes); a window lands where the windows before it in that file end
-        groups: list = []           # [id, [(sequence offset, length, num_kmers, file offset, epilogue, running number)], size]
-        previous_id = None
-        for header, rec_off, rec_len in fa.records:
-            tokens = header.split()
-            seq_id = tokens[0][1:] if tokens else b""       # fasta.py:60-75
-            if rec_len == 0:
-                continue
-            if previous_id != seq_id:
-                if config.include_sequence_ids or config.exclude_sequence_ids:   # search.py:268-278, quirk included
-                    if (seq_id not in config.include_sequence_ids) or (seq_id in config.exclude_sequence_ids):
-                        continue
-                previous_id = seq_id
-                groups.append([seq_id, [], 0])
-            g = groups[-1]
-            for start, length, epilogue in window_plan(rec_len, requested_sequence_length, lookahead_length):
-                num_kmers = length if epilogue else length - lookahead_length
-                segment_number += 1
-                g[1].append((rec_off + start, length, num_kmers, g[2], epilogue, segment_number))
-                g[2] += num_kmers
-        sequence_processed = bool(groups)
+        sequence_processed = bool(plan)
         seen_paths: set = set()
 
         with ThreadPoolExecutor(max_workers=max(1, WRITER_THREADS)) as pool:
             try:
-                for seq_id, wins, total in groups:
+                for seq_id, wins, total in plan:
                     if config.verbose:
                         while inflight:
                             finish(inflight.popleft())
@@ -636,8 +798,8 @@ def _write_unique_counts_device(config: SearchConfig, ix: _lib.Index, data_type,
                     current_fd = os.open(out_path, flags, 0o644)
                     files.append(current_fd)
                     config.log("Writing unique lengths for sequence ID: {}".format(seq_id.decode()))
-                    for n_win, (seq_off, length, num_kmers, offset, epilogue, number) in enumerate(wins):
-                        if number % config.world_size != config.rank:
+                    for n_win, (seq_off, length, num_kmers, offset, is_mine) in enumerate(wins):
+                        if not is_mine:
                             continue
                         config.log("Processing {} k-mers".format(num_kmers))
                         if len(inflight) >= depth:
@@ -685,7 +847,8 @@ def _write_unique_counts_device(config: SearchConfig, ix: _lib.Index, data_type,
         maker.shutdown(wait=True)
         for s_ in slots:
             s_.close()
-        fa.close()
+        if fa is not None:
+            fa.close()
         mark("closed")
         LAST_RUN_TRACE[:] = marks
         if trace:

@@ -70,3 +70,21 @@ def run(rank, world, port, fasta, index, klist, is_range, batch, outdir):
         is_binary_search=is_range, kmer_batch_size=batch, output_directory=Path(outdir), rank=rank, world_size=world))
     dist.barrier()
     dist.destroy_process_group()
+
+
+def run_partitioned(rank, world, port, fasta, index, klist, is_range, batch, outdir):
+    """One rank of a sharded run as a launcher starts it (RANK / WORLD_SIZE / MASTER_* in the environment), all ranks
+    on GPU 0: the real device path with the partitioned ingest (tests/test_gpu_partitioned.py)."""
+    import os
+    os.environ.update(RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK="0", MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port),
+                      NEWMAP_B200_DEVICE="0")
+    from newmap_b200 import search
+    search.INGEST = "device"
+    search.write_unique_counts(search.SearchConfig(
+        fasta_filepaths=[Path(fasta)], fmindex_filepaths=[Path(index)], kmer_lengths=list(klist),
+        is_binary_search=is_range, kmer_batch_size=batch, output_directory=Path(outdir), device=0, rank=rank, world_size=world))
+    trace = dict(search.LAST_RUN_TRACE)
+    assert "exchanged" in trace and "planned" in trace, trace      # the partitioned ingest really ran
+    import torch.distributed as dist
+    dist.barrier()
+    dist.destroy_process_group()

@@ -243,8 +243,8 @@ def test_strict_mode_reports_what_the_default_algorithm_misses(nm, tmp_path):
             outs.append(out.array[:a.size].copy())
         assert np.array_equal(outs[0], outs[1])
         ws.close()
-    for kw, raises in ((dict(), False), (dict(strict=True), True), (dict(algorithm="trajectory"), True)):
-        out = tmp_path / f"o{len(kw)}{raises}"
+    for n, (kw, raises) in enumerate(((dict(), False), (dict(strict=True), True), (dict(algorithm="trajectory"), True))):
+        out = tmp_path / f"out{n}"
         out.mkdir()
         cfg = S.SearchConfig(fasta_filepaths=[bad], fmindex_filepaths=[ixp], kmer_lengths=kl, is_binary_search=True,
                              output_directory=out, **kw)

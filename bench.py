@@ -8,7 +8,7 @@ sharded by 10 M-position segment (the reference's own batching unit), there is n
 collective: torch.distributed is used only for the barrier and the max-over-ranks of the time.
 
 Workload: N = 1 -> c3_1g (BASELINE configs[2], 1 Gbp); N > 1 -> c4_3g (BASELINE configs[3], 3.1 Gbp).
-A step = one pass of the hot path over this rank's `segments_per_step` segments (100 x 10 M positions,
+A step = one pass of the hot path over this rank's `segments_per_step` segments (200 x 10 M positions,
 taken cyclically from the genome starting at rank * segments_per_step: weak scaling).
   value : positions/s with the parsed genome already resident in HBM (CUDA events around K steps)
   e2e   : the same through the C-ABI with pinned HOST buffers, H2D + kernels + D2H every step,
@@ -326,7 +326,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default=None, choices=list(WORKLOADS),
                     help="default: c3_1g on one GPU, c4_3g on several ($NEWMAP_B200_WORKLOAD overrides)")
-    ap.add_argument("--segments-per-step", type=int, default=int(os.environ.get("NEWMAP_B200_SEGMENTS_PER_STEP", "100")))
+    ap.add_argument("--segments-per-step", type=int, default=int(os.environ.get("NEWMAP_B200_SEGMENTS_PER_STEP", "200")))
     ap.add_argument("--cpu-sample", type=int, default=int(os.environ.get("NEWMAP_B200_CPU_SAMPLE", "1000000")))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-job", action="store_true")

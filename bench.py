@@ -48,6 +48,8 @@ WORKLOADS = {
     "c2_100m": "synthetic 100 Mbp single-chromosome genome (BASELINE configs[1] genome), k=20:200",
     "c3_1g": "synthetic 1 Gbp 8-chromosome genome (BASELINE configs[2]), k=20:200",
     "c4_3g": "synthetic 3.1 Gbp 24-sequence genome (BASELINE configs[3]), k=20:200",
+    "c3r_1g": "synthetic 1 Gbp 8-chromosome genome with a mammalian interspersed-repeat spectrum (43 % of it copies of "
+              "diverged repeat families, newmap_b200/synth.py MAMMALIAN_FAMILIES), k=20:200",
 }
 # the reference's index builder (libdivsufsort, one thread, ~11 B of host RAM per base) takes ~40 s per 100 Mbp:
 # used up to this genome size, the GPU builder (same file byte for byte, profiles/r2_index_cmp_*.json) above it
@@ -104,7 +106,7 @@ def prepare_workload(name: str, arm: str = "ours", device: int = 0) -> tuple[Pat
     d.mkdir(parents=True, exist_ok=True)
     lengths, seed = synth.config_lengths(name)
     t0 = time.time()
-    synth.write_fasta(fa, synth.make_genome(lengths, seed))
+    synth.write_fasta(fa, synth.make_genome(lengths, seed, families=synth.MAMMALIAN_FAMILIES if name == "c3r_1g" else None))
     log(f"[bench] genome {name}: {sum(lengths)} bp written in {time.time() - t0:.1f}s")
     builder = os.environ.get("NEWMAP_B200_INDEX_BUILDER", "auto")
     if builder == "auto":
@@ -227,8 +229,14 @@ def cpu_reference_run(fa: Path, ix: Path, steps: int, warmup: int, sample_positi
     cores = min(os.cpu_count() or 1, 255)
     kl = list(range(K_RANGE[0], K_RANGE[1] + 1))
     timer = refdrive.Timer()
+    per_step = None
     for _ in range(warmup):
-        refdrive.search_segment(ix, data, sample_positions, kl, True, 0, True, cores)
+        per_step = _timed(lambda: refdrive.search_segment(ix, data, sample_positions, kl, True, 0, True, cores))
+    # One step costs the same ~16 index re-reads whatever the sample size (1.7 s each for the 3.1 Gbp index): when K steps
+    # would run past the budget, fewer steps are executed -- the figure is a rate, and the line says how many it is over
+    asked, budget = steps, float(os.environ.get("NEWMAP_B200_REF_ARM_BUDGET_S", "420"))
+    if per_step and steps * per_step > budget:
+        steps = max(2, int(budget / per_step))
     t0 = time.perf_counter()
     for _ in range(steps):
         out = refdrive.search_segment(ix, data, sample_positions, kl, True, 0, True, cores, timer)
@@ -241,9 +249,11 @@ def cpu_reference_run(fa: Path, ix: Path, steps: int, warmup: int, sample_positi
     share = min(1.0, sample_positions / BATCH)
     dt_amortised = max(dt - timer.calls * reload_s * (1.0 - share), 1e-9)
     return {"value": sample_positions * steps / dt, "value_amortised": sample_positions * steps / dt_amortised,
-            "seconds": dt, "seconds_amortised": dt_amortised, "cores": cores,
+            "seconds": dt, "seconds_amortised": dt_amortised, "cores": cores, "steps_executed": steps, "steps_asked": asked,
             "index_reload_s_per_call": reload_s, "native_share": timer.native / dt if dt else None,
-            "sample": f"{sample_positions} positions of segment 1 x {steps} step(s), k={K_RANGE[0]}:{K_RANGE[1]}, "
+            "sample": f"{sample_positions} positions of segment 1 x {steps} step(s)"
+                      + (f" (of {asked} asked for: {budget:.0f} s budget)" if steps != asked else "")
+                      + f", k={K_RANGE[0]}:{K_RANGE[1]}, "
                       f"{timer.calls} count_kmers_from_sequence calls, each re-reading the index ({reload_s:.2f}s) as "
                       f"the reference does; value_amortised charges that re-read at the sample's share of a 10M batch",
             "out": out, "data": data}
@@ -356,7 +366,8 @@ def main():
         fa, ix = prepare_workload(workload, arm="reference", device=local)
         r = cpu_reference_run(fa, ix, max(1, args.steps), min(args.warmup, 1), args.cpu_sample)
         line = base_line(workload, world, args.steps, args.warmup, args.k_range, S)
-        line.update(impl="reference", value=r["value"], ms_per_step=1e3 * r["seconds"] / max(1, args.steps),
+        line.update(impl="reference", value=r["value"], ms_per_step=1e3 * r["seconds"] / max(1, r["steps_executed"]),
+                    steps_executed=r["steps_executed"],
                     cpu_baseline={"value": r["value"], "unit": "positions/s", "cores": r["cores"], "kind": "reference",
                                   "sample": r["sample"], "native_share": r["native_share"],
                                   "value_amortised": r["value_amortised"],

@@ -90,6 +90,8 @@ __global__ void __launch_bounds__(kBlock) k_prep(DevIndex ix, SegParams P) {
   __shared__ alignas(128) uint8_t s_raw[kPrepTile + kPrepHalo + 16 + 16];
   __shared__ alignas(8) unsigned long long s_bar;
   __shared__ uint8_t s_code[kPrepTile + kPrepHalo];
+  __shared__ uint8_t s_lut[kBlock];
+  static_assert(kBlock == 256, "one table entry per thread");
   const uint64_t b0 = (uint64_t)blockIdx.x * kPrepTile;                 // first position of the tile
   const uint8_t *src = P.seg + b0;
   const uint32_t head = (uint32_t)(reinterpret_cast<uintptr_t>(src) & 15u);
@@ -106,7 +108,20 @@ __global__ void __launch_bounds__(kBlock) k_prep(DevIndex ix, SegParams P) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(smem_u32(s_raw)), "l"(src - head), "r"(bytes), "r"(bar) : "memory");
   }
-  __syncthreads();   // the barrier is initialised before anyone waits on it
+  // codes of the tile + halo, each computed once, through a 256-entry table (code_of, nm_core.cuh, evaluated once per
+  // byte VALUE and block instead of once per byte): bits 0-6 = letter | irregular | no-start, bit 7 = the byte is 'N'
+  // (the barrier of list mode; range mode: a no-start byte among the first num_kmers positions)
+  {
+    const uint8_t ch = (uint8_t)threadIdx.x;
+    const unsigned l = letter_of(ch);
+    const bool allowed = start_allowed(ch);
+    uint8_t c = (uint8_t)l;
+    if (l == 4u || !allowed) c |= kIrregular;
+    if (!allowed) c |= kNoStart;
+    if (ch == 'N') c |= 0x80;
+    s_lut[threadIdx.x] = c;
+  }
+  __syncthreads();   // the barrier is initialised before anyone waits on it; the table is complete
   if (have) {
     const uint32_t bar = smem_u32(&s_bar);
     uint32_t done = 0;
@@ -115,20 +130,15 @@ __global__ void __launch_bounds__(kBlock) k_prep(DevIndex ix, SegParams P) {
                    : "=r"(done) : "r"(bar) : "memory");
     }
   }
-  // codes of the tile + halo, each computed once
   for (uint32_t j = threadIdx.x; j < kPrepTile + kPrepHalo; j += kBlock) {
     const uint64_t p = b0 + j;
-    uint8_t c = kIrregular;                                             // beyond the segment: invalidates every window that reaches it
+    uint32_t c = kIrregular;                                            // beyond the segment: invalidates every window that reaches it
     if (p < P.seg_len) {
-      const uint8_t ch = s_raw[head + j];
-      const unsigned l = letter_of(ch);
-      const bool allowed = start_allowed(ch);
-      c = (uint8_t)l;
-      if (l == 4u || !allowed) c |= kIrregular;
-      if (!allowed) c |= kNoStart;
-      if ((P.mode == 0) ? (!allowed && p < P.num_kmers) : (ch == 'N')) c |= kBarrier;
+      const uint32_t t = s_lut[s_raw[head + j]];
+      const bool barrier = (P.mode == 0) ? ((t & kNoStart) && p < P.num_kmers) : (t & 0x80u) != 0u;
+      c = (t & 0x7Fu) | (barrier ? (uint32_t)kBarrier : 0u);
     }
-    s_code[j] = c;
+    s_code[j] = (uint8_t)c;
   }
   __syncthreads();
   const uint32_t j0 = threadIdx.x * kPrepV;

@@ -22,9 +22,9 @@ def revcomp(a: np.ndarray) -> np.ndarray:
 
 
 def make_sequence(length: int, rng: np.random.Generator, *, batch: int = 10_000_000,
-                  repeat_scale: float = 1.0, n_runs: bool = True) -> np.ndarray:
-    """One chromosome-like byte array of `length` bases."""
-    seq = _ACGT[rng.integers(0, 4, size=length, dtype=np.uint8)]
+                  repeat_scale: float = 1.0, n_runs: bool = True, background: np.ndarray | None = None) -> np.ndarray:
+    """One chromosome-like byte array of `length` bases (on `background` when given, else on uniform random ACGT)."""
+    seq = background if background is not None else _ACGT[rng.integers(0, 4, size=length, dtype=np.uint8)]
     if length < 64:
         return seq
     # tandem repeats: one every ~1 Mbp (at least one), unit in {2,7,50,171}, 5-50 kb long
@@ -78,9 +78,59 @@ def make_sequence(length: int, rng: np.random.Generator, *, batch: int = 10_000_
     return seq
 
 
-def make_genome(lengths, seed: int, **kw) -> list[tuple[str, np.ndarray]]:
+# interspersed repeats of a mammalian genome, coarsely: SINE-like (300 bp, 11 %), LINE-like (6 kb, truncated copies,
+# 18 %), LTR-like (7 %), DNA-transposon-like (3 %), each old enough to have diverged 8-20 % from its consensus, and a
+# young subfamily of each of the first two (2-3 % divergence): 43 % of the genome in all
+MAMMALIAN_FAMILIES = [(300, 0.09, 0.12, False), (300, 0.02, 0.025, False), (6000, 0.15, 0.15, True),
+                      (6000, 0.03, 0.03, True), (450, 0.07, 0.18, False), (1200, 0.03, 0.20, True)]
+
+
+def make_genome(lengths, seed: int, families=None, **kw) -> list[tuple[str, np.ndarray]]:
     rng = np.random.default_rng(seed)
-    return [(f"chr{i + 1}", make_sequence(int(n), rng, **kw)) for i, n in enumerate(lengths)]
+    out = []
+    for i, n in enumerate(lengths):
+        if families:
+            # interspersed repeats first (one consensus set per genome: the same families on every chromosome), then
+            # the tandem repeats, duplications, soft-masking and N-runs of make_sequence on top
+            base = _ACGT[rng.integers(0, 4, size=int(n), dtype=np.uint8)]
+            fam_rng = np.random.default_rng(seed + 7919)                      # same consensus sequences on every chromosome
+            consensus_state = fam_rng.bit_generator.state
+            add_interspersed_repeats_with_state(base, rng, families, consensus_state)
+            out.append((f"chr{i + 1}", make_sequence(int(n), rng, background=base, **kw)))
+        else:
+            out.append((f"chr{i + 1}", make_sequence(int(n), rng, **kw)))
+    return out
+
+
+def add_interspersed_repeats_with_state(seq, rng, families, consensus_state) -> None:
+    """Overwrites parts of `seq` with copies of repeat families, in place: the repeat spectrum of a mammalian genome
+    (about half of it interspersed repeats, most of them old and diverged) rather than the few young exact repeats
+    make_sequence plants.  families = [(consensus length, fraction of the sequence to cover, divergence, truncate)]:
+    every copy is the family consensus with `divergence` of its bases substituted independently per copy, on either
+    strand; `truncate`: copies keep a random-length 3' part only (like LINE elements).  The consensus sequences come
+    from a generator in `consensus_state`, so that every chromosome of a genome carries the same families."""
+    crng = np.random.default_rng()
+    crng.bit_generator.state = consensus_state
+    n = seq.size
+    for length, fraction, divergence, truncate in families:
+        consensus = _ACGT[crng.integers(0, 4, size=length, dtype=np.uint8)]
+        copies = int(n * fraction / (length * (0.55 if truncate else 1.0)))
+        done = 0
+        while done < copies:
+            m = min(copies - done, max(1, (8 << 20) // length))
+            keep = rng.integers(length // 10, length + 1, size=m) if truncate else np.full(m, length)
+            start = rng.integers(0, max(1, n - length), size=m)
+            col = np.arange(length)[None, :]
+            live = col >= (length - keep)[:, None]
+            piece = np.broadcast_to(consensus, (m, length)).copy()
+            hit = rng.random((m, length)) < divergence
+            piece[hit] = _ACGT[rng.integers(0, 4, size=int(hit.sum()), dtype=np.uint8)]
+            flip = rng.random(m) < 0.5
+            piece[flip] = _COMP[piece[flip][:, ::-1]]
+            live[flip] = live[flip][:, ::-1]
+            pos = start[:, None] + col
+            seq[pos[live]] = piece[live]
+            done += m
 
 
 def write_fasta(path, records, width: int = 60) -> None:
@@ -114,4 +164,7 @@ def config_lengths(name: str) -> tuple[list[int], int]:
         return [int(x) for x in (w / w.sum() * 1_000_000_000)], 1000
     if name == "c4_3g":
         return [int(x) for x in GRCH38_FRACTIONS * 3_100_000_000], 3100
+    if name == "c3r_1g":     # c3_1g's shape with the interspersed-repeat spectrum of a mammalian genome (MAMMALIAN_FAMILIES)
+        w = np.array([5, 4, 3.5, 3, 2.5, 2, 1.5, 1.0])
+        return [int(x) for x in (w / w.sum() * 1_000_000_000)], 1001
     raise KeyError(name)

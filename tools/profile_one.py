@@ -1,5 +1,5 @@
 """Short single-GPU program for ncu: a few searches of one 10 M-position segment of a bench
-workload (default c2_100m).  `python tools/profile_one.py [workload] [repeats] [algo]`."""
+workload (default c2_100m).  `python tools/profile_one.py [workload] [repeats] [algo] [segment] [k range]`."""
 import sys
 from pathlib import Path
 
@@ -12,14 +12,17 @@ from newmap_b200 import _lib  # noqa: E402
 workload = sys.argv[1] if len(sys.argv) > 1 else "c2_100m"
 repeats = int(sys.argv[2]) if len(sys.argv) > 2 else 3
 algo = sys.argv[3] if len(sys.argv) > 3 else "auto"
+segment = int(sys.argv[4]) if len(sys.argv) > 4 else 1
+krange = sys.argv[5] if len(sys.argv) > 5 else "20:200"
+bench.K_RANGE = tuple(int(x) for x in krange.split(":"))
 fa, ixp = bench.prepare_workload(workload)
-seg, n = bench.sample_segment(fa, 1)
+seg, n = bench.sample_segment(fa, segment)
 ix = _lib.Index(ixp, device=0)
 ws = _lib.Workspace(ix, len(seg.data))
 pb = _lib.PinnedBuffer(len(seg.data))
 pb.array[:] = np.frombuffer(seg.data, dtype=np.uint8)
 ws.upload(pb.ptr, len(seg.data))
-kl = list(range(20, 201))
+kl = list(range(bench.K_RANGE[0], bench.K_RANGE[1] + 1))
 for _ in range(repeats):
     ws.search(n, kl, True, algo=algo, out_width=1)
     st = ws.sync()

@@ -147,7 +147,7 @@ int nm_workspace_sync(nm_workspace *ws, nm_stats *stats);
                              start the chains from the file's seed table instead of the derived one; default 0 */
 #define NM_OPT_DCAP 2     /* first-pass depth cap of the trajectory-free search, characters; 0 = seed depth in use + 3 (derived
                              table) or + 12 (the file's table) */
-#define NM_OPT_GSIZE 3    /* positions per certificate group; 0 = 20 */
+#define NM_OPT_GSIZE 3    /* positions per certificate group; 0 = 40 */
 #define NM_OPT_PASS1 4    /* kernel of the first pass: 0 = chosen from the seed depth in use (default), 1 = one thread per
                              position, 2 = tiled (seed lookups batched, lanes refilled from a queue) */
 #define NM_OPT_GSIZE2 5   /* positions per group of the coarse certificate round that runs before the fine one (one chain,

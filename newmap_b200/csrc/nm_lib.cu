@@ -720,7 +720,7 @@ int nm_workspace_search(nm_workspace *ws, uint64_t num_kmers, int mode, const ui
     //  steps are inside repeats, where the certificate pass settles 20 positions with one chain)
     P.dcap = ws->opt_dcap ? ws->opt_dcap : (deep ? sl + 3 : sl + 12);
     if (P.dcap <= sl) P.dcap = sl + 1;
-    P.gsize = ws->opt_gsize ? ws->opt_gsize : 20;  // profiles/r1_gsize_sweep_final_c3_1g.jsonl
+    P.gsize = ws->opt_gsize ? ws->opt_gsize : 40;  // profiles/r2_sweep_f_gsize.jsonl (round 1, dense first pass: 20)
     P.own_chains = ws->opt_own_chains == ~0u ? nm::kCertOwnChains : ws->opt_own_chains;
     P.cert_runs = ws->opt_cert_runs ? ws->opt_cert_runs : nm::kCertRuns;
     // only when passes 2 and 3 will run (run_search: deep_passes).  Off by default: with 2 it removes 45 % of the first

@@ -346,7 +346,7 @@ def main():
                          "line then says so in metric and config.k_range")
     ap.add_argument("--pool", type=int, default=int(os.environ.get("NEWMAP_B200_POOL", "10")),
                     help="workspaces (one CUDA stream each) the device-resident arm deals its segments over")
-    ap.add_argument("--e2e-depth", type=int, default=int(os.environ.get("NEWMAP_B200_E2E_DEPTH", "4")),
+    ap.add_argument("--e2e-depth", type=int, default=int(os.environ.get("NEWMAP_B200_E2E_DEPTH", "8")),
                     help="workspaces (streams) the end-to-end arm pipelines over")
     args = ap.parse_args()
 
@@ -605,6 +605,22 @@ def main():
             probe_indep[g] = max(_lib.probe_random_access(local, 2 << 30, g, 2 << 20, 32, 8, False)[0],
                                  _lib.probe_random_access(local, 2 << 30, g, 8 << 20, 32, 4, False)[0])
         achieved = bytes_dom / (dom_ms * 1e-3) / 1e9 if dom_ms else None
+        # the whole step as it really runs (kernels of several segments overlapped across streams): DRAM bytes per segment
+        # from the ncu capture of every kernel of a search (profiles/traffic.json) over the timed region's time per segment
+        whole_step = None
+        if tf.is_file():
+            t = json.loads(tf.read_text()).get(workload, {})
+            seg_bytes = sum(v for k, v in t.items() if k.startswith("k_") and isinstance(v, (int, float)))
+            if seg_bytes and not args.k_range:
+                ms_seg = ms_value / args.steps / S
+                whole_step = {"dram_bytes_per_segment_ncu": seg_bytes, "ms_per_segment_pipelined": ms_seg,
+                              "achieved": seg_bytes / (ms_seg * 1e-3) / 1e9, "unit": "GB/s",
+                              "frac_of_streaming_peak": seg_bytes / (ms_seg * 1e-3) / 1e9 / hbm_peak,
+                              "random_accesses_per_s": seg_bytes / 64 / (ms_seg * 1e-3),
+                              "frac_of_random_access_ceiling": seg_bytes / 64 / (ms_seg * 1e-3) / (probe_indep[64] or 1),
+                              "how": "every DRAM byte of one search (ncu, one segment) / time per segment of the timed region; "
+                                     "ceiling = independent random 64-byte accesses per second measured in this run (a DRAM "
+                                     "sector miss fetches its 64-byte pair)"}
         line = base_line(workload, world, args.steps, args.warmup, args.k_range, S)
         line.update({
             "value": positions_all * args.steps / (ms_value * 1e-3),
@@ -635,6 +651,7 @@ def main():
                                           "seed_lookups_per_position": seeds / max(1, iso_positions),
                                           "lf_steps_pass1_per_position": lf1 / max(1, iso_positions),
                                           "seed_lookups_pass1_per_position": seeds1 / max(1, iso_positions)},
+                         "whole_step": whole_step,
                          "seed_depth": iso[0]["seed_depth"] if iso else None,
                          "ref_trajectory_lf_steps_per_position": st_traj.lf_steps / max(1, n0),
                          "random_sector_probe": {"dependent_loads_per_s": probe, "independent_loads_per_s": probe_indep,

@@ -86,6 +86,10 @@ __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)_
 
 __global__ void __launch_bounds__(kBlock) k_prep(DevIndex ix, SegParams P) {
   (void)ix;
+  // the counters of the search that follows start here (no separate copy: a 128-byte host-to-device copy would queue
+  // behind the 10 MB segment uploads of the other workspaces on the copy engine)
+  if (blockIdx.x == 0 && threadIdx.x < CTR_N)
+    P.counters[threadIdx.x] = (threadIdx.x == CTR_ZERO_KEY || threadIdx.x == CTR_MINLEN) ? ~0ull : 0ull;
   // raw bytes of the tile from the 16-byte-aligned address at or below its first byte: head (<= 15) + tile + halo
   __shared__ alignas(128) uint8_t s_raw[kPrepTile + kPrepHalo + 16 + 16];
   __shared__ alignas(8) unsigned long long s_bar;

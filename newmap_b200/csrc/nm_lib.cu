@@ -305,8 +305,11 @@ int run_search(nm_workspace *ws, int algo) {
   nm_index *ix = ws->ix;
   nm::SegParams &P = ws->P;
   cudaStream_t st = ws->stream;
-  static const unsigned long long init_counters[nm::CTR_N] = {0, 0, 0, 0, ~0ull, 0, 0, 0, 0, 0, 0, 0, ~0ull, 0, 0, 0};
-  NM_CUDA(cudaMemcpyAsync(ws->d_counters, init_counters, sizeof init_counters, cudaMemcpyHostToDevice, st));
+  // (the counters are reset by block 0 of k_prep; an empty segment launches no kernel at all)
+  if (P.seg_len == 0) {
+    static const unsigned long long init_counters[nm::CTR_N] = {0, 0, 0, 0, ~0ull, 0, 0, 0, 0, 0, 0, 0, ~0ull, 0, 0, 0};
+    NM_CUDA(cudaMemcpyAsync(ws->d_counters, init_counters, sizeof init_counters, cudaMemcpyHostToDevice, st));
+  }
   NM_CUDA(cudaEventRecord(ws->ev[EV_H2D1], st));
   nm::launch_prep(ix->dev, P, st);
   ws->launches = P.seg_len ? 1u : 0u;

@@ -37,6 +37,7 @@ extern "C" {
 #define NM_EARG (-6)       /* invalid argument (empty k-mer, index+length beyond the sequence, ...) */
 #define NM_ECUDA (-7)      /* CUDA runtime error; nm_last_cuda_error() has the text */
 #define NM_EUNSUPPORTED (-8)
+#define NM_ELIMIT (-9)     /* request larger than the fixed scratch of nm_count_from_sequence_noalloc */
 
 #define NM_MODE_RANGE 0    /* klist = {min_k, max_k}: minimum over every k in [min_k, max_k] */
 #define NM_MODE_LIST 1     /* klist = explicit lengths, tried in the order given */
@@ -121,6 +122,22 @@ int nm_index_set_seed_depth(nm_index *ix, uint32_t depth);
 int nm_count_from_sequence(nm_index *ix, const uint8_t *seq, uint64_t seq_len, const uint64_t *idx,
                            const uint64_t *len, uint64_t n, int reverse_complement, uint32_t *counts,
                            uint64_t *lf_steps);
+
+/* The same counts as nm_count_from_sequence (same arguments, same results, same NM_EARG rule) WITHOUT ANY ALLOCATION:
+ * no cudaMalloc / cudaFree / allocating library routine is called.  (No counterpart in the reference: added
+ * for callers that cannot allocate -- code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it.)  nm_count_from_sequence allocates five device buffers per call; here the device
+ * copies of seq / idx / len, the counts and the LF-step counter live in ONE fixed array of
+ * NM_NOALLOC_SCRATCH_BYTES of device memory inside the library (a file-scope `static __device__` array: every GPU
+ * that loads the library holds it until the process exits).  A request needs 256 + 20 * round_up(n, 64) +
+ * round_up(seq_len + 16, 256) bytes of it; a larger one is refused with NM_ELIMIT and nothing is launched.
+ * Every call on a device shares that array: the calls of one process are serialised by the library and each call
+ * clears what it needs to start at zero, but work that another process or stream of the caller's makes overlap with a
+ * call on the same GPU through the same array would race -- do not alias it. */
+#define NM_NOALLOC_SCRATCH_BYTES (4u << 20)
+int nm_count_from_sequence_noalloc(nm_index *ix, const uint8_t *seq, uint64_t seq_len, const uint64_t *idx,
+                                   const uint64_t *len, uint64_t n, int reverse_complement, uint32_t *counts,
+                                   uint64_t *lf_steps);
 
 /* One segment buffer of search.py (data = num_kmers start positions + look-ahead):
  * out[i], i < num_kmers, = minimum unique length or 0, written as uint8/16/32 (out_width 1/2/4).

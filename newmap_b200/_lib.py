@@ -17,7 +17,8 @@ LIB_PATH = Path(os.environ.get("NEWMAP_B200_LIB") or PKG_DIR / "libnewmap_b200.s
 NM_MODE_RANGE, NM_MODE_LIST = 0, 1
 NM_ALGO_AUTO, NM_ALGO_TRAJECTORY, NM_ALGO_FREE_GENERIC = 0, 1, 2
 ALGOS = {"auto": NM_ALGO_AUTO, "trajectory": NM_ALGO_TRAJECTORY, "free_generic": NM_ALGO_FREE_GENERIC}
-NM_EOPEN, NM_EFORMAT, NM_EVERSION, NM_EALLOC, NM_ESHORT, NM_EARG, NM_ECUDA, NM_EUNSUPPORTED = range(-1, -9, -1)
+NM_EOPEN, NM_EFORMAT, NM_EVERSION, NM_EALLOC, NM_ESHORT, NM_EARG, NM_ECUDA, NM_EUNSUPPORTED, NM_ELIMIT = range(-1, -10, -1)
+NM_NOALLOC_SCRATCH_BYTES = 4 << 20
 
 
 class IndexInfo(C.Structure):
@@ -66,6 +67,7 @@ SIGNATURES = {
     "nm_index_info_get": (_i, [_vp, C.POINTER(IndexInfo)]),
     "nm_index_set_seed_depth": (_i, [_vp, _u32]),
     "nm_count_from_sequence": (_i, [_vp, _vp, _u64, _vp, _vp, _u64, _i, _vp, C.POINTER(_u64)]),
+    "nm_count_from_sequence_noalloc": (_i, [_vp, _vp, _u64, _vp, _vp, _u64, _i, _vp, C.POINTER(_u64)]),
     "nm_min_unique": (_i, [_vp, _vp, _u64, _u64, _i, _vp, _u32, _u32, _i, _i, _i, _vp, C.POINTER(Stats)]),
     "nm_workspace_create": (_i, [_vp, _u64, _vp, C.POINTER(_vp)]),
     "nm_workspace_destroy": (None, [_vp]),
@@ -225,8 +227,10 @@ class Index:
     def bwt_length(self) -> int:
         return int(self.info.bwt_length)
 
-    def count(self, seq, idx, length, reverse_complement: bool = False, return_steps: bool = False):
-        """u32 occurrence counts of seq[idx[q]:idx[q]+length[q]] (nm_count_from_sequence)."""
+    def count(self, seq, idx, length, reverse_complement: bool = False, return_steps: bool = False,
+              no_alloc: bool = False):
+        """u32 occurrence counts of seq[idx[q]:idx[q]+length[q]] (nm_count_from_sequence; no_alloc: the variant that
+        calls no cudaMalloc and refuses requests beyond its fixed scratch with ValueError)."""
         s = as_u8(seq)
         idx = np.ascontiguousarray(idx, dtype=np.uint64)
         length = np.ascontiguousarray(length, dtype=np.uint64)
@@ -234,8 +238,11 @@ class Index:
             raise ValueError("Both lists of indices and lengths must be the same length")
         out = np.zeros(idx.size, dtype=np.uint32)
         steps = _u64(0)
-        rc = load().nm_count_from_sequence(self._h, s.ctypes.data, s.size, idx.ctypes.data, length.ctypes.data,
-                                           idx.size, int(reverse_complement), out.ctypes.data, C.byref(steps))
+        fn = load().nm_count_from_sequence_noalloc if no_alloc else load().nm_count_from_sequence
+        rc = fn(self._h, s.ctypes.data, s.size, idx.ctypes.data, length.ctypes.data,
+                idx.size, int(reverse_complement), out.ctypes.data, C.byref(steps))
+        if rc == NM_ELIMIT:
+            raise ValueError(load().nm_strerror(rc).decode())
         if rc == NM_EARG:
             if np.any(length == 0):
                 raise ValueError("All elements of the kmer list must have non-zero length")

@@ -418,6 +418,7 @@ const char *nm_strerror(int code) {
     case NM_EARG: return "invalid argument";
     case NM_ECUDA: return "CUDA error";
     case NM_EUNSUPPORTED: return "unsupported";
+    case NM_ELIMIT: return "request exceeds the fixed scratch of the no-allocation entry point (NM_NOALLOC_SCRATCH_BYTES)";
     default: return "unknown error";
   }
 }
@@ -946,6 +947,75 @@ int nm_probe_random_access(int device, uint64_t bytes, uint32_t granule, uint64_
   cudaFree(buf);
   cudaFree(sink);
   return rc;
+}
+
+// ---------------------------------------------------------------------------------------------
+// nm_count_from_sequence without any allocation (include/newmap_b200.h,
+// no counterpart in the reference).  The scratch nm_count_from_sequence cudaMallocs per call -- device copies of
+// the sequence, the query lists, the counts and the counters -- lives in one file-scope device array.  In HOST code
+// the array's name is only a stand-in for the symbol, not a device address: the address is asked for once per
+// device, with that device current (cudaGetSymbolAddress), and that pointer is what the kernel gets.
+// ---------------------------------------------------------------------------------------------
+}  // extern "C"
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NM_NOALLOC_SCRATCH_BYTES];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_noalloc_mu;                       // one call at a time per process: every call shares the array
+unsigned char *g_noalloc_ptr[kMaxDevices];     // device address of g_noalloc_scratch on each device, once known
+
+int noalloc_scratch(int device, unsigned char **out) {
+  if (device < 0 || device >= kMaxDevices) return NM_EARG;
+  if (!g_noalloc_ptr[device]) {
+    void *p = nullptr;
+    NM_CUDA(cudaGetSymbolAddress(&p, g_noalloc_scratch));   // (the caller has made `device` current)
+    g_noalloc_ptr[device] = static_cast<unsigned char *>(p);
+  }
+  *out = g_noalloc_ptr[device];
+  return NM_OK;
+}
+}  // namespace
+
+extern "C" {
+
+int nm_count_from_sequence_noalloc(nm_index *ix, const uint8_t *seq, uint64_t seq_len, const uint64_t *idx,
+                                   const uint64_t *len, uint64_t n, int reverse_complement, uint32_t *counts,
+                                   uint64_t *lf_steps) {
+  if (!ix || (n && (!idx || !len || !counts)) || (seq_len && !seq)) return NM_EARG;
+  for (uint64_t q = 0; q < n; ++q)  // newmap-count.c:63-68,184-190
+    if (len[q] == 0 || idx[q] > seq_len || len[q] > seq_len - idx[q]) return NM_EARG;
+  if (n == 0) return NM_OK;
+  // layout: [counters, 256 B][idx, 8 B x n64][len, 8 B x n64][counts, 4 B x n64][sequence + 16]
+  if (n > NM_NOALLOC_SCRATCH_BYTES || seq_len > NM_NOALLOC_SCRATCH_BYTES) return NM_ELIMIT;
+  const uint64_t n64 = (n + 63) / 64 * 64;
+  const uint64_t seq_bytes = (seq_len + 16 + 255) / 256 * 256;
+  if (256 + 20 * n64 + seq_bytes > NM_NOALLOC_SCRATCH_BYTES) return NM_ELIMIT;
+  std::lock_guard<std::mutex> all(g_noalloc_mu);
+  std::lock_guard<std::mutex> lock(ix->mu);
+  NM_CUDA(cudaSetDevice(ix->device));
+  unsigned char *base = nullptr;
+  const int rc = noalloc_scratch(ix->device, &base);
+  if (rc != NM_OK) return rc;
+  unsigned long long *d_ctr = reinterpret_cast<unsigned long long *>(base);
+  uint64_t *d_idx = reinterpret_cast<uint64_t *>(base + 256);
+  uint64_t *d_len = d_idx + n64;
+  uint32_t *d_counts = reinterpret_cast<uint32_t *>(d_len + n64);
+  uint8_t *d_seq = reinterpret_cast<uint8_t *>(d_counts + n64);
+  static_assert(nm::CTR_N * 8 <= 256, "the counters fit the first 256 bytes of the scratch");
+  NM_CUDA(cudaMemsetAsync(d_ctr, 0, 256, 0));   // the array keeps the last call's contents: the counters start at zero
+  NM_CUDA(cudaMemcpyAsync(d_seq, seq, seq_len, cudaMemcpyHostToDevice, 0));
+  NM_CUDA(cudaMemcpyAsync(d_idx, idx, n * 8, cudaMemcpyHostToDevice, 0));
+  NM_CUDA(cudaMemcpyAsync(d_len, len, n * 8, cudaMemcpyHostToDevice, 0));
+  nm::launch_count(ix->dev, d_seq, d_idx, d_len, n, reverse_complement != 0, d_counts, d_ctr, 0);
+  NM_CUDA(cudaGetLastError());
+  NM_CUDA(cudaMemcpy(counts, d_counts, n * 4, cudaMemcpyDeviceToHost));
+  if (lf_steps) {
+    unsigned long long v = 0;
+    NM_CUDA(cudaMemcpy(&v, d_ctr + nm::CTR_LF, 8, cudaMemcpyDeviceToHost));
+    *lf_steps += v;
+  }
+  return NM_OK;
 }
 
 }  // extern "C"

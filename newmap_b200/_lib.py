@@ -289,7 +289,8 @@ class Workspace:
 
     def close(self):
         if getattr(self, "_h", None):
-            load().nm_workspace_destroy(self._h)
+            if getattr(self.index, "_h", None):      # (an index closed first took the device context of its workspaces'
+                load().nm_workspace_destroy(self._h)   #  owner with it: the handle is dropped, not dereferenced)
             self._h = None
 
     def __del__(self):

@@ -32,6 +32,8 @@ def open_index(index_path, device: int | None = None, seed_depth: int | None = N
 
 
 def close_all() -> None:
+    from . import search
+    search.release_cached_slots()          # workspaces must go before their index
     with _cache_lock:
         for ix in _cache.values():
             ix.close()

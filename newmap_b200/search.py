@@ -678,8 +678,8 @@ def _write_unique_counts_device(config: SearchConfig, ix: _lib.Index, data_type,
     fa = None
     # workspaces and pinned output buffers are allocated while the file is being read
     maker = ThreadPoolExecutor(max_workers=1)
-    made = maker.submit(lambda: [_DeviceSlot(ix, requested_sequence_length, itemsize)
-                                 for _ in range(DEVICE_PIPELINE_DEPTH + max(2, WRITER_THREADS - 1))])
+    made = maker.submit(_take_slots, ix, requested_sequence_length, itemsize,
+                        DEVICE_PIPELINE_DEPTH + max(2, WRITER_THREADS - 1))
     try:
         partitioned = None
         if (sharded and PARTITIONED and path.suffix != ".gz" and os.environ.get("MASTER_ADDR")
@@ -734,12 +734,9 @@ def _write_unique_counts_device(config: SearchConfig, ix: _lib.Index, data_type,
         depth = 1 if config.verbose else DEVICE_PIPELINE_DEPTH
         min_kmer_length = min(config.kmer_lengths)
         totals = dict(ambiguous=0, unique=0, none=0, max_len=min_kmer_length, min_len=max_kmer_length)
-        if config.verbose:
-            for s_ in slots:
-                s_.ws.option("out_stats", 1)
-        if config.strict:
-            for s_ in slots:
-                s_.ws.option("strict", 1)
+        for s_ in slots:                       # (slots may come from an earlier run of this process: set both ways)
+            s_.ws.option("out_stats", 1 if config.verbose else 0)
+            s_.ws.option("strict", 1 if config.strict else 0)
 
         def write_out(slot, fd, nbytes, offset, truncate_to):
             os.pwrite(fd, memoryview(slot.out.array)[:nbytes], offset)
@@ -845,14 +842,53 @@ def _write_unique_counts_device(config: SearchConfig, ix: _lib.Index, data_type,
         except Exception:
             pass
         maker.shutdown(wait=True)
-        for s_ in slots:
-            s_.close()
+        _return_slots(ix, requested_sequence_length, itemsize, slots)
         if fa is not None:
             fa.close()
         mark("closed")
         LAST_RUN_TRACE[:] = marks
         if trace:
             print("[newmap_b200 ingest] " + ", ".join(f"{n} {t:.3f}s" for n, t in marks), file=sys.stderr, flush=True)
+
+
+# Workspaces + pinned output buffers of the device path, kept between the runs of one process (a resident index
+# stays resident; so does its scratch): 11 slots are 110 cudaMalloc calls and 110 MB of page-locked memory, which
+# costs more than searching a chromosome -- and page-locking serialises between the ranks of a node.
+# NEWMAP_B200_SLOT_CACHE=0 frees them after every run.
+SLOT_CACHE = os.environ.get("NEWMAP_B200_SLOT_CACHE", "1") != "0"
+_slot_cache: dict = {}
+
+
+def _take_slots(ix: _lib.Index, max_seg_len: int, itemsize: int, count: int) -> list:
+    slots = _slot_cache.pop((id(ix), ix._h.value if ix._h else 0, max_seg_len, itemsize), []) if SLOT_CACHE else []
+    for s_ in slots:
+        s_.job = s_.pending = None
+    while len(slots) < count:
+        slots.append(_DeviceSlot(ix, max_seg_len, itemsize))
+    return slots
+
+
+def _return_slots(ix: _lib.Index, max_seg_len: int, itemsize: int, slots: list) -> None:
+    if SLOT_CACHE and ix._h:
+        for old in _slot_cache.values():            # one set at a time: another index or shape replaces it
+            for s_ in old:
+                s_.close()
+        _slot_cache.clear()
+        _slot_cache[(id(ix), ix._h.value, max_seg_len, itemsize)] = slots
+    else:
+        for s_ in slots:
+            s_.close()
+
+
+def release_cached_slots() -> None:
+    for old in _slot_cache.values():
+        for s_ in old:
+            s_.close()
+    _slot_cache.clear()
+
+
+import atexit  # noqa: E402
+atexit.register(release_cached_slots)
 
 
 class _DeviceSlot:

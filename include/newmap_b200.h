@@ -175,7 +175,7 @@ int nm_workspace_sync(nm_workspace *ws, nm_stats *stats);
 #define NM_OPT_STALL 7    /* first pass: a chain whose interval kept its size for this many steps in a row is left to the
                              later passes at once instead of at the depth cap (it is inside a repeat); default 0 = off */
 #define NM_OPT_CERT_RUNS 8 /* certificate pass: runs of consecutive unsettled positions a thread takes per group and strand
-                             (one anchor chain each; the rest goes to the third pass); 0 = default 4 */
+                             (one anchor chain each; the rest goes to the third pass); 0 = default 1 */
 #define NM_OPT_STRIDE 9   /* sparse first pass: at most this many positions per unconditional seed-table lookup (the rest is
                              settled by upper bounds spread from it, or by chains of their own); 0 = as many as the slack
                              between the table depth and the shortest length allows (at most 8), 1 = every window */

@@ -1053,7 +1053,7 @@ NM_HD void cert_run_rc(const DevIndex &ix, const uint32_t *C32, const SegParams 
 // the dcap positions after each difference between the copies (those were settled by the first pass), so a group no
 // wider than dcap holds one run and a wider one holds a few.  Each run gets its own anchor chain; at most kCertRuns
 // runs per group and strand are taken, the rest stays deep for the third pass.
-constexpr uint32_t kCertRuns = 4;  // default of P.cert_runs
+constexpr uint32_t kCertRuns = 1;  // default of P.cert_runs (profiles/r2_sweep_i_cert_runs.jsonl; 4 with groups of 20 in round 1)
 NM_HD void free_cert_thread(const DevIndex &ix, const uint32_t *C32, const SegParams &P, uint32_t t, uint32_t &steps,
                             uint32_t &seeds, uint32_t parts = 3u) {
   const uint32_t gs = P.gsize;

@@ -132,6 +132,11 @@ def base_line(workload: str, world: int, steps: int, warmup: int, k_range: str |
                        "segments_per_step_per_gpu": segments_per_step,
                        "l2": "no flush: every step streams segments_per_step x 10 MB of sequence and random-reads an "
                              "index (rank32 + seed table, 70 GB) far larger than the 126 MB L2"}}
+    if world > 1 and workload == "c4_3g":
+        # N = 1 runs BASELINE configs[2] (1 Gbp), N > 1 configs[3] (3.1 Gbp): a ratio of the two lines mixes a change of
+        # genome with the scaling.  The single-GPU figure for THIS genome, for whoever wants the scaling alone:
+        line["config"]["same_workload_on_one_gpu"] = ("15.7 G positions/s resident on c4_3g with 1 GPU "
+                                                      "(profiles/r2_sweep_i_cert_runs.jsonl); 18.9 G on c3_1g, the N=1 line")
     if k_range:
         line["metric"] = f"genome positions/sec, min-unique-k search k={k_range}"
         line["config"]["k_range"] = k_range

@@ -48,6 +48,7 @@ INGEST = os.environ.get("NEWMAP_B200_INGEST", "auto")
 # a run sharded by its launcher (torchrun: RANK / WORLD_SIZE / MASTER_ADDR) reads, per rank, only the part of an
 # uncompressed FASTA its windows lie in; 0 = every rank reads and parses the whole text
 PARTITIONED = os.environ.get("NEWMAP_B200_PARTITIONED", "1") != "0"
+INTERLEAVE = int(os.environ.get("NEWMAP_B200_INTERLEAVE", "8"))    # sequences whose windows are dealt round-robin (device path)
 # [(phase name, seconds since the start of the run)] of the last device-ingest run of this process (bench.py reads it)
 LAST_RUN_TRACE: list = []
 
@@ -767,7 +768,16 @@ def _write_unique_counts_device(config: SearchConfig, ix: _lib.Index, data_type,
 
         with ThreadPoolExecutor(max_workers=max(1, WRITER_THREADS)) as pool:
             try:
-                for seq_id, wins, total in plan:
+                def settle_writes():
+                    while inflight:
+                        finish(inflight.popleft())
+                    for s_ in slots:
+                        if s_.pending is not None:
+                            s_.pending.result()
+                            s_.pending = None
+
+                def open_group(seq_id):
+                    nonlocal current_sequence_id
                     if config.verbose:
                         while inflight:
                             finish(inflight.popleft())
@@ -782,38 +792,54 @@ def _write_unique_counts_device(config: SearchConfig, ix: _lib.Index, data_type,
                         if sharded:
                             raise ValueError(f"sequence id {seq_id.decode()!r} appears again after another sequence: "
                                              "not supported when the run is sharded over several ranks")
-                        while inflight:
-                            finish(inflight.popleft())
-                        for s_ in slots:
-                            if s_.pending is not None:
-                                s_.pending.result()
-                                s_.pending = None
+                        settle_writes()
                     seen_paths.add(out_path)
+                    if len(files) >= 256:           # many sequences: no more than a few hundred files open at a time
+                        settle_writes()
+                        for fd_ in files:
+                            os.close(fd_)
+                        files.clear()
                     # one rank: truncate like search.py:305.  Several ranks share the file: create without truncating
                     # (another rank may already have written its windows); the owner of the last window sets the size.
                     flags = os.O_RDWR | os.O_CREAT | (0 if sharded else os.O_TRUNC)
-                    current_fd = os.open(out_path, flags, 0o644)
-                    files.append(current_fd)
+                    fd_ = os.open(out_path, flags, 0o644)
+                    files.append(fd_)
                     config.log("Writing unique lengths for sequence ID: {}".format(seq_id.decode()))
-                    for n_win, (seq_off, length, num_kmers, offset, is_mine) in enumerate(wins):
-                        if not is_mine:
-                            continue
-                        config.log("Processing {} k-mers".format(num_kmers))
-                        if len(inflight) >= depth:
-                            finish(inflight.popleft())
-                        slot = next((s for s in slots if s.job is None and (s.pending is None or s.pending.done())), None)
-                        if slot is None:
-                            slot = next(s for s in slots if s.job is None)
-                        if slot.pending is not None:
-                            slot.pending.result()
-                            slot.pending = None
-                        slot.job = (seq_off, length, num_kmers, current_fd, offset, n_win == len(wins) - 1)
-                        slot.ws.attach(fa, seq_off, length)
-                        slot.ws.search(num_kmers, config.kmer_lengths, config.is_binary_search,
-                                       config.initial_search_length, config.use_reverse_complement, config.algorithm,
-                                       itemsize)
-                        slot.ws.download(slot.out.ptr)
-                        inflight.append(slot)
+                    return fd_
+
+                def submit(fd_, window, last_of_file):
+                    seq_off, length, num_kmers, offset, _ = window
+                    config.log("Processing {} k-mers".format(num_kmers))
+                    if len(inflight) >= depth:
+                        finish(inflight.popleft())
+                    slot = next((s for s in slots if s.job is None and (s.pending is None or s.pending.done())), None)
+                    if slot is None:
+                        slot = next(s for s in slots if s.job is None)
+                    if slot.pending is not None:
+                        slot.pending.result()
+                        slot.pending = None
+                    slot.job = (seq_off, length, num_kmers, fd_, offset, last_of_file)
+                    slot.ws.attach(fa, seq_off, length)
+                    slot.ws.search(num_kmers, config.kmer_lengths, config.is_binary_search,
+                                   config.initial_search_length, config.use_reverse_complement, config.algorithm,
+                                   itemsize)
+                    slot.ws.download(slot.out.ptr)
+                    inflight.append(slot)
+
+                # Windows of the same sequence land in the same file, and buffered writes to one file serialise in the
+                # kernel (the inode lock): the writer threads only work side by side when the windows in flight belong
+                # to different files.  So the windows of up to INTERLEAVE sequences are dealt round-robin -- every
+                # window knows its file offset, the order is free -- unless the log must follow the reference's order
+                # (--verbose) or an id comes back after another one (the file is then truncated in between).
+                ids = [seq_id for seq_id, _, _ in plan]
+                group = 1 if (config.verbose or len(set(ids)) != len(ids)) else max(1, INTERLEAVE)
+                for g0 in range(0, len(plan), group):
+                    batch = plan[g0:g0 + group]
+                    fds = [open_group(seq_id) for seq_id, _, _ in batch]
+                    for n_win in range(max(len(wins) for _, wins, _ in batch)):
+                        for fd_, (_, wins, _) in zip(fds, batch):
+                            if n_win < len(wins) and wins[n_win][4]:
+                                submit(fd_, wins[n_win], n_win == len(wins) - 1)
                 mark("all_segments_launched")
                 while inflight:
                     finish(inflight.popleft())

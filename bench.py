@@ -136,7 +136,7 @@ def base_line(workload: str, world: int, steps: int, warmup: int, k_range: str |
         # N = 1 runs BASELINE configs[2] (1 Gbp), N > 1 configs[3] (3.1 Gbp): a ratio of the two lines mixes a change of
         # genome with the scaling.  The single-GPU figure for THIS genome, for whoever wants the scaling alone:
         line["config"]["same_workload_on_one_gpu"] = ("15.7 G positions/s resident on c4_3g with 1 GPU "
-                                                      "(profiles/r2_sweep_i_cert_runs.jsonl); 18.9 G on c3_1g, the N=1 line")
+                                                      "(profiles/r2_sweep_i_cert_runs.jsonl); the N=1 line of bench.py is c3_1g")
     if k_range:
         line["metric"] = f"genome positions/sec, min-unique-k search k={k_range}"
         line["config"]["k_range"] = k_range

@@ -667,6 +667,15 @@ def main():
                                           "lf_steps_pass1_per_position": lf1 / max(1, iso_positions),
                                           "seed_lookups_pass1_per_position": seeds1 / max(1, iso_positions)},
                          "whole_step": whole_step,
+                         # the same figure for each kernel of the search that walks the index (one search at a time)
+                         "per_kernel": {
+                             name: {"ms_per_launch": ms_k / nsearch, "algorithmic_bytes_per_launch": b_k / nsearch,
+                                    "achieved": (b_k / (ms_k * 1e-3) / 1e9) if ms_k else None,
+                                    "frac": (b_k / (ms_k * 1e-3) / 1e9 / hbm_peak) if ms_k else None}
+                             for name, ms_k, b_k in (
+                                 ("k_pass1_sparse" if deep else "k_free_chain(first)", ms_pass1, lf1 * 64 + seeds1 * 32),
+                                 ("k_free_cert", ms_cert, ((lf - lf1) * 64 + (seeds - seeds1) * 32) * ms_cert / max(ms_cert + ms_pass3, 1e-9)),
+                                 ("k_free_chain", ms_pass3, ((lf - lf1) * 64 + (seeds - seeds1) * 32) * ms_pass3 / max(ms_cert + ms_pass3, 1e-9)))},
                          "seed_depth": iso[0]["seed_depth"] if iso else None,
                          "ref_trajectory_lf_steps_per_position": st_traj.lf_steps / max(1, n0),
                          "random_sector_probe": {"dependent_loads_per_s": probe, "independent_loads_per_s": probe_indep,

@@ -729,7 +729,6 @@ def _write_unique_counts_device(config: SearchConfig, ix: _lib.Index, data_type,
         inflight: deque = deque()
         files: list = []
         current_sequence_id = None
-        current_fd = -1
         # --verbose: the log lines come in the reference's order (a segment is finished before the next one is
         # announced) and the statistics of search.py:318-347 come from a reduction on the device
         depth = 1 if config.verbose else DEVICE_PIPELINE_DEPTH

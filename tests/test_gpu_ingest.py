@@ -190,3 +190,31 @@ def test_verbose_statistics_come_from_the_device(nm, tmp_path, monkeypatch, caps
         logs[ingest] = capsys.readouterr().err.splitlines()
     assert logs["host"] == logs["device"]
     assert any("unique lengths found" in t for t in logs["device"]) and any("Processing 1500 k-mers" in t for t in logs["device"])
+
+
+@pytest.mark.skipif(not ora.ref_available(), reason="needs oracle/_ref (the reference's index builder)")
+def test_many_sequences_interleaved_writes(nm, tmp_path, monkeypatch):
+    """More sequences than the device path deals round-robin at a time (INTERLEAVE = 8), of very different lengths,
+    some shorter than a window: same files as the host path, which writes file after file; and with the interleaving
+    off and the number of files open at a time bounded."""
+    from newmap_b200 import search as S
+    rng = np.random.default_rng(23)
+    acgt = np.frombuffer(b"ACGTN", dtype=np.uint8)
+    parts = []
+    for j in range(21):
+        n = int(rng.integers(5, 9000)) if j % 5 else 30
+        parts.append(b">s%d\n" % j + acgt[rng.integers(0, 5 if j % 3 == 0 else 4, n)].tobytes() + b"\n")
+    fa = tmp_path / "many.fa"
+    fa.write_bytes(b"".join(parts))
+    ixp = tmp_path / "many.awfmi"
+    ora.ref_build_index(fa, ixp, 8, 5)
+    kw = dict(kmer_lengths=list(range(12, 61)), is_binary_search=True, kmer_batch_size=700)
+    a = _run_search(tmp_path, "many", fa, ixp, "host", monkeypatch, **kw)
+    b = _run_search(tmp_path, "many", fa, ixp, "device", monkeypatch, **kw)
+    assert a.keys() == b.keys() and len(a) == 21
+    assert a == b
+    monkeypatch.setattr(S, "INTERLEAVE", 1)
+    assert _run_search(tmp_path, "many_il1", fa, ixp, "device", monkeypatch, **kw) == a
+    monkeypatch.setattr(S, "INTERLEAVE", 5)
+    monkeypatch.setattr(S, "SLOT_CACHE", False)
+    assert _run_search(tmp_path, "many_il5", fa, ixp, "device", monkeypatch, **kw) == a

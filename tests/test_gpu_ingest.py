@@ -9,6 +9,7 @@ import pytest
 
 from conftest import GOLD
 from newmap_b200.fasta import _records
+from oracle import ora
 
 pytestmark = pytest.mark.gpu
 

@@ -94,6 +94,13 @@ NM_HD void atomic_max64(unsigned long long *p, unsigned long long v) {
   if (v > *p) *p = v;
 #endif
 }
+NM_HD void atomic_or32(uint32_t *p, uint32_t v) {
+#if defined(__CUDA_ARCH__)
+  atomicOr(p, v);
+#else
+  *p |= v;
+#endif
+}
 NM_HD void atomic_or64(unsigned long long *p, unsigned long long v) {
 #if defined(__CUDA_ARCH__)
   atomicOr(p, v);
@@ -380,6 +387,8 @@ struct SegParams {
   uint32_t *tile_first;  // ceil(seg_len / kTile): first barrier of the tile, or kNoBarrier
   uint32_t *G;           // seg_len + 1: length of the shortest unique suffix ending at e (forward strand)
   uint32_t *R;           // seg_len: shortest length from i at which the other strand has no match
+  uint32_t *deepmap;     // (seg_len + 1) bits, cleared by prep: bit p = the first pass left G[p] or R[p] kDeep.  Deep entries are
+                         // 1-2 % of a segment: passes 2 and 3 look here before they read G / R at all (nullptr: they scan)
   void *out;             // num_kmers entries of out_width bytes
   const uint32_t *klist; // list mode: nk lengths in the order given
   unsigned long long *counters;  // CTR_N slots
@@ -793,11 +802,26 @@ NM_HD bool rc_wanted(const SegParams &P, uint32_t i) {
   return P.use_rc && i < P.num_kmers && !(P.codes[i] & kNoStart);
 }
 
+NM_HD void mark_deep(const SegParams &P, uint32_t p) {
+  if (P.deepmap) atomic_or32(&P.deepmap[p >> 5], 1u << (p & 31u));
+}
+NM_HD bool maybe_deep(const SegParams &P, uint32_t p) {
+  return !P.deepmap || ((ld32(P.deepmap + (p >> 5)) >> (p & 31u)) & 1u);
+}
+// any position of [lo, hi] marked?  (whole words are looked at: a neighbour's bit only costs the scan it would have saved)
+NM_HD bool maybe_deep_range(const SegParams &P, uint32_t lo, uint32_t hi) {
+  if (!P.deepmap) return true;
+  for (uint32_t w = lo >> 5; w <= (hi >> 5); ++w)
+    if (ld32(P.deepmap + w)) return true;
+  return false;
+}
+
 // pass 1 and pass 3 share this: `cap` = P.dcap in pass 1, kmax in pass 3 (which only redoes kDeep entries)
 // (parts: bit 0 = the forward-strand chain ending at p, bit 1 = the other-strand chain starting at p)
 NM_HD void free_chain_thread(const DevIndex &ix, const uint32_t *C32, const SegParams &P, uint32_t p, bool first,
                              uint32_t &steps, uint32_t &seeds, uint32_t parts = 3u) {
   const uint32_t cap = first ? (P.dcap < P.kmax ? P.dcap : P.kmax) : P.kmax;
+  if (!first && !maybe_deep(P, p)) return;
   if ((parts & 1u) && (first || P.G[p] == kDeep)) {
     uint32_t g = kNone;
     if (fwd_wanted(P, p)) {
@@ -805,6 +829,7 @@ NM_HD void free_chain_thread(const DevIndex &ix, const uint32_t *C32, const SegP
                 : chain_value(P, run_fwd_chain(ix, C32, P, p, cap, steps, seeds), cap, kNone);
     }
     P.G[p] = g;
+    if (g == kDeep) mark_deep(P, p);
   }
   if ((parts & 2u) && p < P.seg_len && (first || P.R[p] == kDeep)) {
     uint32_t rr = kInf;
@@ -813,6 +838,7 @@ NM_HD void free_chain_thread(const DevIndex &ix, const uint32_t *C32, const SegP
                  : chain_value(P, run_rc_chain(ix, C32, P, p, cap, steps, seeds), cap, kInf);
     }
     P.R[p] = rr;
+    if (rr == kDeep) mark_deep(P, p);
   }
 }
 
@@ -918,6 +944,7 @@ NM_HD void sparse_side_thread(const DevIndex &ix, const uint32_t *C32, const Seg
     while (sparse_next_fwd(P, cur, last)) {
       const uint32_t v = run_chain_pass1(ix, C32, P, 0u, cur, cap, kNone, steps, seeds);
       P.G[cur] = v;
+      if (v == kDeep) mark_deep(P, cur);
       cur = sparse_spread_fwd(P, cur, last, v);
     }
   } else {
@@ -926,6 +953,7 @@ NM_HD void sparse_side_thread(const DevIndex &ix, const uint32_t *C32, const Seg
     while (sparse_next_rc(P, first, end1)) {
       const uint32_t v = run_chain_pass1(ix, C32, P, 1u, end1 - 1u, cap, kInf, steps, seeds);
       P.R[end1 - 1u] = v;
+      if (v == kDeep) mark_deep(P, end1 - 1u);
       end1 = sparse_spread_rc(P, first, end1, v);
     }
   }
@@ -1061,6 +1089,12 @@ NM_HD void free_cert_thread(const DevIndex &ix, const uint32_t *C32, const SegPa
     const uint32_t first = t * gs + 1;
     uint32_t last = first + gs - 1;
     if (last > P.seg_len) last = P.seg_len;
+    if (first > last || !maybe_deep_range(P, first, last)) parts &= ~1u;
+  }
+  if (parts & 1u) {
+    const uint32_t first = t * gs + 1;
+    uint32_t last = first + gs - 1;
+    if (last > P.seg_len) last = P.seg_len;
     // (the r-th runs of the lanes of a warp are taken in the same iteration of this loop, so their chains run side by
     // side; with the chain inside the scanning loop each lane would reach it in another iteration, one after the other)
     uint32_t budget = P.own_chains, e = first;
@@ -1077,6 +1111,7 @@ NM_HD void free_cert_thread(const DevIndex &ix, const uint32_t *C32, const SegPa
     const uint32_t first = t * gs;
     uint32_t end = first + gs;
     if (end > P.num_kmers) end = P.num_kmers;
+    if (first >= end || !maybe_deep_range(P, first, end - 1u)) return;
     uint32_t budget = P.own_chains, i = first;
     for (uint32_t r = 0; r < P.cert_runs; ++r) {
       while (i < end && P.R[i] != kDeep) ++i;

@@ -90,6 +90,12 @@ __global__ void __launch_bounds__(kBlock) k_prep(DevIndex ix, SegParams P) {
   // behind the 10 MB segment uploads of the other workspaces on the copy engine)
   if (blockIdx.x == 0 && threadIdx.x < CTR_N)
     P.counters[threadIdx.x] = (threadIdx.x == CTR_ZERO_KEY || threadIdx.x == CTR_MINLEN) ? ~0ull : 0ull;
+  // ... and so does the map of positions the first pass leaves deep: every block clears the words of its own tile
+  // (the grid covers seg_len + 32 positions, so the word of the end position seg_len is someone's)
+  if (P.deepmap && threadIdx.x < kPrepTile / 32) {
+    const uint64_t w = (uint64_t)blockIdx.x * (kPrepTile / 32) + threadIdx.x;
+    if (w <= ((uint64_t)P.seg_len >> 5)) P.deepmap[w] = 0u;
+  }
   // raw bytes of the tile from the 16-byte-aligned address at or below its first byte: head (<= 15) + tile + halo
   __shared__ alignas(128) uint8_t s_raw[kPrepTile + kPrepHalo + 16 + 16];
   __shared__ alignas(8) unsigned long long s_bar;
@@ -253,6 +259,7 @@ __global__ void __launch_bounds__(kBlock, NM_P1_MINB) k_pass1_sparse(DevIndex ix
   // the value v of `pos` is known: store it, spread the bounds it gives, find the side's next position that needs a
   // chain.  true = the side goes on at `pos` (updated); false = the side is finished
   auto settle = [&](uint32_t kind, uint32_t &pos, uint32_t limit, uint32_t v) -> bool {
+    if (v == kDeep) mark_deep(P, pos);
     if (kind == 0u) {
       P.G[pos] = v;
       uint32_t cur = sparse_spread_fwd(P, pos, limit, v);

@@ -56,7 +56,7 @@ struct nm_workspace {
   // device buffers
   uint8_t *d_seg = nullptr, *d_codes = nullptr;
   const uint8_t *seg_ext = nullptr;  // segment attached from a parsed FASTA (nm_workspace_attach) instead of uploaded
-  uint32_t *d_pk = nullptr, *d_tile_first = nullptr, *d_G = nullptr, *d_R = nullptr;
+  uint32_t *d_pk = nullptr, *d_tile_first = nullptr, *d_G = nullptr, *d_R = nullptr, *d_deepmap = nullptr;
   uint64_t *d_barmask = nullptr;
   uint8_t *d_sub = nullptr;  // candidates for lengths below the table depth (allocated by the first search that needs it)
   void *d_out = nullptr;
@@ -282,6 +282,7 @@ int ws_alloc(nm_workspace *ws) {
   NM_CUDA(cudaMalloc((void **)&ws->d_codes, n + 16));
   NM_CUDA(cudaMalloc((void **)&ws->d_pk, (n / 16 + 4) * 4));
   NM_CUDA(cudaMalloc((void **)&ws->d_barmask, ntiles * 8));
+  NM_CUDA(cudaMalloc((void **)&ws->d_deepmap, (n / 32 + 4) * 4));
   NM_CUDA(cudaMalloc((void **)&ws->d_tile_first, ntiles * 4));
   NM_CUDA(cudaMalloc((void **)&ws->d_G, (n + 2) * 4));
   NM_CUDA(cudaMalloc((void **)&ws->d_R, (n + 1) * 4));
@@ -552,6 +553,7 @@ void nm_workspace_destroy(nm_workspace *ws) {
   cudaFree(ws->d_codes);
   cudaFree(ws->d_pk);
   cudaFree(ws->d_barmask);
+  cudaFree(ws->d_deepmap);
   cudaFree(ws->d_sub);
   cudaFree(ws->d_tile_first);
   cudaFree(ws->d_G);
@@ -681,6 +683,7 @@ int nm_workspace_search(nm_workspace *ws, uint64_t num_kmers, int mode, const ui
   P.codes = ws->d_codes;
   P.pk = ws->d_pk;
   P.barmask = ws->d_barmask;
+  P.deepmap = ws->d_deepmap;
   P.tile_first = ws->d_tile_first;
   P.G = ws->d_G;
   P.R = ws->d_R;

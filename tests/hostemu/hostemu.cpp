@@ -109,8 +109,10 @@ int emu_min_unique(EmuIndex *ix, const uint8_t *seg, uint32_t seg_len, uint32_t 
   std::vector<uint8_t> codes(seg_len + 16);
   std::vector<uint32_t> pk(seg_len / 16 + 2), tf((seg_len + kTile - 1) / kTile + 1), G(seg_len + 2), R(seg_len + 1);
   std::vector<uint64_t> barmask((seg_len + kTile - 1) / kTile + 1);
+  std::vector<uint32_t> deepmap(seg_len / 32 + 4, 0u);   // cleared by k_prep on the device
   unsigned long long ctr[CTR_N] = {0, 0, 0, 0, ~0ull, 0, 0, 0};
   SegParams P{};
+  P.deepmap = (gsize + dcap) % 3 == 2 ? nullptr : deepmap.data();   // (without the map passes 2 and 3 scan G / R: same results)
   P.seg = seg; P.codes = codes.data(); P.pk = pk.data(); P.barmask = barmask.data(); P.tile_first = tf.data();
   P.G = G.data(); P.R = R.data(); P.out = out; P.klist = klist; P.counters = ctr;
   P.seg_len = seg_len; P.num_kmers = num_kmers; P.nk = nk; P.initial = initial; P.mode = mode;
